@@ -1,0 +1,161 @@
+/*
+ * ptb200.h — C-ABI of the B200 path-trace device shim (libptb200.so).
+ *
+ * This is the drop-in boundary of the hot path.  The reference host
+ * (/root/reference/main.cpp) talks to its device only through a small subset
+ * of the OpenCL 1.x C++ wrapper; every entry point below replaces one of those
+ * call sites (cited as main.cpp:line) or one kernel of prog.cl (prog.cl:line).
+ * A header-only `CL/cl.hpp` look-alike (opencl_path_tracer_b200/shim/CL/cl.hpp)
+ * forwards the cl:: classes to these functions, so main.cpp compiles and runs
+ * unchanged on top of them.  INTEGRATION.md shows the binding.
+ *
+ * Conventions (mirroring how the reference uses OpenCL):
+ *   - plain C types only; 0 == PTB_SUCCESS == CL_SUCCESS, negative = error.
+ *   - the reference ignores almost every return code (main.cpp:506-682), so an
+ *     error is also recorded in a sticky per-process string (ptb_last_error)
+ *     and printed to stderr once; later calls become no-ops returning the error.
+ *   - one in-order stream per process (the reference has one in-order
+ *     cl::CommandQueue, main.cpp:506); one process drives one GPU.
+ *   - buffer layouts are the reference's kernel ABI structs, byte for byte
+ *     (prog.cl:1-35 / main.cpp:92-348): Material 80 B, Ray 32 B, Triangle 80 B,
+ *     Node 48 B, Camera 80 B, colors float3 = 16 B per pixel, rnds int per pixel.
+ *   - there is NO CPU fallback: without a CUDA device ptb_init fails.
+ */
+#ifndef PTB200_H_
+#define PTB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTB_SUCCESS 0
+#define PTB_ERR_NO_DEVICE (-1)     /* CL_DEVICE_NOT_FOUND                       */
+#define PTB_ERR_INVALID_VALUE (-30)/* CL_INVALID_VALUE                          */
+#define PTB_ERR_INVALID_MEM (-38)  /* CL_INVALID_MEM_OBJECT                     */
+#define PTB_ERR_INVALID_KERNEL (-46)/* CL_INVALID_KERNEL_NAME                   */
+#define PTB_ERR_INVALID_ARGS (-52) /* CL_INVALID_KERNEL_ARGS                    */
+#define PTB_ERR_OUT_OF_MEMORY (-4) /* CL_MEM_OBJECT_ALLOCATION_FAILURE          */
+#define PTB_ERR_DEVICE (-9999)     /* a CUDA runtime call failed (see last_error)*/
+
+/* Opaque buffer handle; 0 is the null handle.  Replaces cl::Buffer / cl::ImageGL. */
+typedef uint64_t ptb_mem;
+
+/* Kernel ids.  Replace cl::Kernel(program,"gen_ray"|"trace_ray") (main.cpp:637,647)
+ * and the never-launched "filt_im" (main.cpp:665-668, prog.cl:391-427). */
+enum { PTB_KERNEL_GEN_RAY = 0, PTB_KERNEL_TRACE_RAY = 1, PTB_KERNEL_FILT_IM = 2, PTB_KERNEL_COUNT = 3 };
+
+/* ---- bring-up: replaces cl::Platform::get / getDevices / cl::Context /
+ *      cl::Program::build / cl::CommandQueue (main.cpp:460-506).  Kernels are
+ *      AOT-compiled for sm_100a, so "build" is a no-op that reports success. ---- */
+int ptb_init(int device_ordinal);          /* idempotent; -1 = take LOCAL_RANK / device 0 */
+int ptb_shutdown(void);                    /* frees every buffer and the accel structure */
+/* replaces the clGetDeviceInfo dump of Scene::list_info (main.cpp:389-455).
+ * what: 0 name, 1 hardware version, 2 driver version, 3 "language" version, 4 extensions */
+int ptb_device_string(int what, char *dst, size_t cap);
+int ptb_device_compute_units(void);        /* CL_DEVICE_MAX_COMPUTE_UNITS → SM count */
+const char *ptb_backend_name(void);        /* "cuda-sm100a" for the product library */
+
+/* ---- memory: replaces cl::Buffer(context, flags, bytes) (main.cpp:508,509,520,619,623,627,632),
+ *      cl::ImageGL (main.cpp:519) and blocking enqueueWriteBuffer (main.cpp:526,620,624,628,633).
+ *      Handles are reference counted like cl::Memory. ---- */
+ptb_mem ptb_alloc(size_t bytes);
+ptb_mem ptb_alloc_image(int width, int height); /* W×H RGBA float image, headless stand-in for the GL texture */
+int ptb_retain(ptb_mem m);
+int ptb_release(ptb_mem m);
+int ptb_write(ptb_mem m, size_t offset, size_t bytes, const void *src);   /* blocking */
+int ptb_read(ptb_mem m, size_t offset, size_t bytes, void *dst);          /* blocking; the reference's read-back is dead code (main.cpp:690,728) */
+size_t ptb_mem_size(ptb_mem m);
+/* extensions for hosts that own device memory already (torch tensors, NCCL buffers) */
+ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes);  /* non-owning handle */
+void *ptb_device_ptr(ptb_mem m);
+
+/* ---- kernels: replaces cl::Kernel::setArg (main.cpp:638-640, 648-660) and
+ *      enqueueNDRangeKernel / finish (main.cpp:642,674,675,678,680).
+ *      Argument lists are prog.cl:384-386 (gen_ray) and prog.cl:292-304 (trace_ray). ---- */
+int ptb_kernel_id(const char *name);       /* "gen_ray" → 0, "trace_ray" → 1, "filt_im" → 2, else <0 */
+int ptb_set_arg(int kernel, int index, size_t bytes, const void *value);  /* by-value args: int, Camera */
+int ptb_set_arg_mem(int kernel, int index, ptb_mem m);                    /* buffer / image args      */
+int ptb_launch(int kernel, size_t global_x, size_t global_y);             /* asynchronous, in order   */
+int ptb_finish(void);
+const char *ptb_last_error(void);          /* "" when no error so far */
+void ptb_clear_error(void);
+
+/* ---- extensions beyond the reference surface (all optional for a drop-in host) ---- */
+
+/* Closest-hit structure used by trace_ray / ptb_render. */
+enum {
+    PTB_ACCEL_AUTO = 0,        /* brute force for tiny scenes, LBVH otherwise                         */
+    PTB_ACCEL_BRUTE = 1,       /* first_intersect over all triangles (prog.cl:113-122, :318)            */
+    PTB_ACCEL_REFBVH = 2,      /* the uploaded Node[]/kd_tree_shift as is (prog.cl:144-184)             */
+    PTB_ACCEL_LBVH = 3         /* GPU-built Morton LBVH, == brute force incl. index tie-break           */
+};
+/* Arithmetic variant of the path kernels. */
+enum {
+    PTB_MATH_PARITY = 0,       /* no FMA contraction, IEEE div/sqrt, op order of prog.cl                */
+    PTB_MATH_FAST = 1          /* FMA, hoisted reciprocals, precomputed edge planes                     */
+};
+/* Kernel organisation of ptb_render. */
+enum {
+    PTB_PIPE_MEGAKERNEL = 0,   /* one persistent kernel, path regeneration inside the loop              */
+    PTB_PIPE_WAVEFRONT = 1     /* generate / intersect / shade kernels over compacted ray queues        */
+};
+int ptb_set_accel(int accel);
+int ptb_set_math(int math);
+int ptb_set_pipeline(int pipe);
+int ptb_get_accel(void);       /* the structure the next launch will really use (AUTO resolved)         */
+int ptb_build_accel(void);     /* force the (lazy) staging + LBVH build now; returns when done          */
+
+/* In-kernel sample loop: renders `spp` further samples of every pixel with the
+ * arguments currently set on trace_ray (args 1-6, 8-12; `rays` is not needed),
+ * starting at sample index trace_ray.arg10 and advancing the per-pixel RNG
+ * states exactly as `spp` pairs of gen_ray+trace_ray launches would
+ * (main.cpp:683-687).  colors[] receives the same running mean (prog.cl:379).
+ * The image argument (arg 0) is written once at the end when present. */
+int ptb_render(int spp);
+
+/* Restrict the next launches to a pixel subset — the multi-GPU tile split
+ * (rank r of n renders interleaved groups of `group` consecutive pixel ids:
+ * id/group % n == r).  n==1 restores the full image. */
+int ptb_set_pixel_shard(int rank, int nranks, int group);
+/* spp-split support: accumulate plain per-pixel sums (not the running mean) so
+ * ranks can be added: colors[id] += sample; combine with ptb_resolve_sum. */
+int ptb_set_accumulate_sum(int on);
+int ptb_resolve_sum(ptb_mem colors_sum, int total_spp); /* colors = sum / total_spp in place */
+
+/* Work counters of the launches since the last reset.  rays = bounce-loop
+ * iterations executed (prog.cl:317-319); box/tri tests only with ptb_set_count_work(1). */
+typedef struct {
+    uint64_t rays;
+    uint64_t box_tests;
+    uint64_t tri_tests;
+    uint64_t tri_stage1, tri_stage2, tri_stage3; /* tests that got past t<0 / edge 1 / edge 2 (prog.cl:100-106) */
+    uint64_t pixel_samples;
+} ptb_counters;
+int ptb_set_count_work(int on);
+int ptb_get_counters(ptb_counters *out);   /* synchronises the stream */
+int ptb_reset_counters(void);
+
+/* Output resolve: tone map prog.cl:247-269 on the linear colors buffer.
+ * mode 0 = reinhard+sRGB (what trace_ray writes to the texture, prog.cl:380),
+ * mode 1 = filmic (prog.cl:259-263).  Writes W*H RGBA8 (top row first, i.e. flipped:
+ * the reference image is bottom-up, prog.cl:86-88) into host memory. L==0 maps to black
+ * (the reference produces NaN there, prog.cl:265-268). */
+int ptb_resolve_rgba8(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host);
+/* 3x3 median denoise of prog.cl:391-427 as a standalone pass: colors → image (RGBA float). */
+int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height);
+
+/* Stream sharing with a host framework (torch): the shim launches on this CUDA stream. */
+int ptb_set_stream(void *cuda_stream);     /* NULL = the shim's own stream */
+void *ptb_get_stream(void);
+/* LBVH statistics of the last build: nodes, leaves, max depth, build milliseconds. */
+int ptb_accel_stats(int *n_nodes, int *n_tris, int *max_depth, float *build_ms);
+/* number of kernels launched by this library since init (bench.py gpu_launches) */
+uint64_t ptb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB200_H_ */
