@@ -105,6 +105,14 @@ enum {
 int ptb_set_accel(int accel);
 int ptb_set_math(int math);
 int ptb_set_pipeline(int pipe);
+/* The reference enqueues gen_ray then trace_ray for every sample (main.cpp:683-687).  With fusion on
+ * (the default) a gen_ray launch is deferred and folded into the trace_ray launch that follows it on
+ * the same rays/rnds buffers, so the primary rays never travel through rays[] (it is scratch in the
+ * reference: rewritten by gen_ray every sample, read by nobody else).  Any read, write, finish or
+ * differing launch in between runs the deferred gen_ray as its own kernel first.  0 = run the two
+ * kernels literally.  Results are identical either way. */
+int ptb_set_fuse_gen(int on);
+int ptb_set_lbvh_leaf(int max_tris); /* 1..8 triangles per LBVH leaf (default 4); takes effect at the next build */
 int ptb_get_accel(void);       /* the structure the next launch will really use (AUTO resolved)         */
 int ptb_build_accel(void);     /* force the (lazy) staging + LBVH build now; returns when done          */
 

@@ -1,0 +1,321 @@
+// lbvh.cu — GPU construction of the closest-hit structure used by the LBVH traversal in
+// pt_kernels.cuh.  New to this implementation: the reference builds one median-split tree per OBJ
+// shape on the host (main.cpp:195-304, 536-551) and walks them one after the other
+// (prog.cl:144-184); here ONE tree over all uploaded triangles is built on the device:
+//
+//   1. k_bounds     centroid box + largest |coordinate| (block reduce + ordered-int atomics)
+//   2. k_morton     63-bit Morton code of the triangle's box centre (21 bits per axis)
+//   3. cub radix sort of (code, upload index) — stable, so equal codes keep upload order
+//   4. k_gather     triangles re-laid in Morton order (3 float4 planes) + their boxes
+//   5. k_hierarchy  Karras 2012 radix tree over the sorted codes (ties split on the index bits)
+//   6. k_refit      bottom-up boxes, second arrival at a node (atomic counter) continues upward
+//   7. k_emit       64-byte traversal nodes holding BOTH children's (inflated) boxes and links;
+//                   a subtree with <= leaf_size triangles becomes one leaf [first, first+count)
+//   8. k_depth      depth of the emitted tree (the traversal stack is bounded; checked by the host)
+//
+// Node layout (4 x float4, Aila–Laine style):
+//   n0 = (L.lo.x, L.hi.x, L.lo.y, L.hi.y)  n1 = (R.lo.x, R.hi.x, R.lo.y, R.hi.y)
+//   n2 = (L.lo.z, L.hi.z, R.lo.z, R.hi.z)  n3 = (bits(left link), bits(right link), 0, 0)
+// link >= 0: node index.  link < 0: leaf, ~link = (first << 3) | (count-1) in Morton order.
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "lbvh.h"
+
+namespace {
+
+__device__ __forceinline__ unsigned f2ord(float f) {
+    unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(unsigned u) {
+    unsigned b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+
+struct Box {
+    float lo[3], hi[3];
+};
+__device__ __forceinline__ Box tri_box(float4 a, float4 b, float4 c) {
+    Box r;
+    r.lo[0] = fminf(a.x, fminf(b.x, c.x)); r.hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
+    r.lo[1] = fminf(a.y, fminf(b.y, c.y)); r.hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
+    r.lo[2] = fminf(a.z, fminf(b.z, c.z)); r.hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    return r;
+}
+
+// bounds[0..2] = min centre, [3..5] = max centre (ordered-uint), [6] = max |coordinate|
+__global__ void k_bounds(const float4 *q0, const float4 *q1, const float4 *q2, int n, unsigned *bounds) {
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, mabs = 0.0f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        Box b = tri_box(q0[i], q1[i], q2[i]);
+        for (int k = 0; k < 3; ++k) {
+            float c = 0.5f * (b.lo[k] + b.hi[k]);
+            if (c == c && fabsf(c) < 1e30f) { lo[k] = fminf(lo[k], c); hi[k] = fmaxf(hi[k], c); }
+            float m = fmaxf(fabsf(b.lo[k]), fabsf(b.hi[k]));
+            if (m < 1e30f) mabs = fmaxf(mabs, m);
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+        mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(bounds + k, f2ord(lo[k]));
+            atomicMax(bounds + 3 + k, f2ord(hi[k]));
+        }
+        atomicMax(bounds + 6, f2ord(mabs));
+    }
+}
+
+__device__ __forceinline__ unsigned long long spread21(unsigned v) {
+    unsigned long long x = v & 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void k_morton(const float4 *q0, const float4 *q1, const float4 *q2, int n, const unsigned *bounds,
+                         unsigned long long *keys, int *vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Box b = tri_box(q0[i], q1[i], q2[i]);
+    unsigned g[3];
+    for (int k = 0; k < 3; ++k) {
+        float lo = ord2f(bounds[k]), hi = ord2f(bounds[3 + k]);
+        float c = 0.5f * (b.lo[k] + b.hi[k]);
+        float ext = hi - lo;
+        float u = ext > 0.0f ? (c - lo) / ext : 0.0f;
+        if (!(u >= 0.0f)) u = 0.0f;         // NaN / below → 0
+        if (u > 1.0f) u = 1.0f;
+        double s = (double)u * 2097151.0;    // 2^21 - 1
+        g[k] = (unsigned)s;
+    }
+    keys[i] = (spread21(g[0]) << 2) | (spread21(g[1]) << 1) | spread21(g[2]);
+    vals[i] = i;
+}
+
+__global__ void k_gather(const float4 *q0, const float4 *q1, const float4 *q2, const int *vals, int n,
+                         float4 *sq0, float4 *sq1, float4 *sq2, float4 *leaf_lo, float4 *leaf_hi) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int i = vals[pos];
+    float4 a = q0[i], b = q1[i], c = q2[i];
+    sq0[pos] = a; sq1[pos] = b; sq2[pos] = c;
+    Box bx = tri_box(a, b, c);
+    leaf_lo[pos] = make_float4(bx.lo[0], bx.lo[1], bx.lo[2], 0.0f);
+    leaf_hi[pos] = make_float4(bx.hi[0], bx.hi[1], bx.hi[2], 0.0f);
+}
+
+// common-prefix length of sorted keys i and j; equal codes fall back to the position bits (Karras 2012 §4)
+__device__ __forceinline__ int delta(const unsigned long long *keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((unsigned)i ^ (unsigned)j);
+    return __clzll((long long)(a ^ b));
+}
+
+// internal node i ∈ [0, n-2]: range, split, children (child >= 0 internal, < 0 → ~leaf position), parents
+__global__ void k_hierarchy(const unsigned long long *keys, int n, int2 *range, int2 *child, int *parent_of_node, int *parent_of_leaf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int first = min(i, j), last = max(i, j);
+    int left = (first == gamma) ? ~gamma : gamma;
+    int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    range[i] = make_int2(first, last);
+    child[i] = make_int2(left, right);
+    if (left >= 0) parent_of_node[left] = i; else parent_of_leaf[~left] = i;
+    if (right >= 0) parent_of_node[right] = i; else parent_of_leaf[~right] = i;
+    if (i == 0) parent_of_node[0] = -1;
+}
+
+__global__ void k_refit(int n, const int2 *child, const int *parent_of_node, const int *parent_of_leaf,
+                        const float4 *leaf_lo, const float4 *leaf_hi, float4 *node_lo, float4 *node_hi, int *arrivals) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int node = parent_of_leaf[pos];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(arrivals + node, 1) == 0) return;   // the sibling subtree is not finished yet
+        __threadfence();
+        int2 c = child[node];
+        // volatile reads: the sibling's box was written by another thread in this launch
+        const volatile float4 *llo = c.x >= 0 ? node_lo + c.x : leaf_lo + ~c.x;
+        const volatile float4 *lhi = c.x >= 0 ? node_hi + c.x : leaf_hi + ~c.x;
+        const volatile float4 *rlo = c.y >= 0 ? node_lo + c.y : leaf_lo + ~c.y;
+        const volatile float4 *rhi = c.y >= 0 ? node_hi + c.y : leaf_hi + ~c.y;
+        float4 lo = make_float4(fminf(llo->x, rlo->x), fminf(llo->y, rlo->y), fminf(llo->z, rlo->z), 0.0f);
+        float4 hi = make_float4(fmaxf(lhi->x, rhi->x), fmaxf(lhi->y, rhi->y), fmaxf(lhi->z, rhi->z), 0.0f);
+        volatile float4 *olo = node_lo + node, *ohi = node_hi + node;
+        olo->x = lo.x; olo->y = lo.y; olo->z = lo.z; olo->w = 0.0f;
+        ohi->x = hi.x; ohi->y = hi.y; ohi->z = hi.z; ohi->w = 0.0f;
+        node = parent_of_node[node];
+    }
+}
+
+__device__ __forceinline__ int leaf_link(int first, int count) { return ~((first << 3) | (count - 1)); }
+
+__global__ void k_emit(int n, int leaf_size, float eps, const int2 *range, const int2 *child,
+                       const float4 *leaf_lo, const float4 *leaf_hi, const float4 *node_lo, const float4 *node_hi, float4 *bvh) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 rg = range[i];
+    if (rg.y - rg.x + 1 <= leaf_size && i != 0) return;   // inside a collapsed leaf: never visited
+    int2 c = child[i];
+    float4 lo[2], hi[2];
+    int link[2];
+    int cc[2] = {c.x, c.y};
+    for (int k = 0; k < 2; ++k) {
+        if (cc[k] >= 0) {
+            lo[k] = node_lo[cc[k]]; hi[k] = node_hi[cc[k]];
+            int2 cr = range[cc[k]];
+            int cnt = cr.y - cr.x + 1;
+            link[k] = cnt <= leaf_size ? leaf_link(cr.x, cnt) : cc[k];
+        } else {
+            lo[k] = leaf_lo[~cc[k]]; hi[k] = leaf_hi[~cc[k]];
+            link[k] = leaf_link(~cc[k], 1);
+        }
+        lo[k].x -= eps; lo[k].y -= eps; lo[k].z -= eps;
+        hi[k].x += eps; hi[k].y += eps; hi[k].z += eps;
+    }
+    bvh[4 * i + 0] = make_float4(lo[0].x, hi[0].x, lo[0].y, hi[0].y);
+    bvh[4 * i + 1] = make_float4(lo[1].x, hi[1].x, lo[1].y, hi[1].y);
+    bvh[4 * i + 2] = make_float4(lo[0].z, hi[0].z, lo[1].z, hi[1].z);
+    bvh[4 * i + 3] = make_float4(__int_as_float(link[0]), __int_as_float(link[1]), 0.0f, 0.0f);
+}
+
+// depth of every triangle's leaf in the EMITTED tree = number of emitted ancestors
+__global__ void k_depth(int n, int leaf_size, const int2 *range, const int *parent_of_node, const int *parent_of_leaf, int *max_depth, int *n_emitted) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    int depth = 0;
+    if (pos < n) {
+        for (int node = parent_of_leaf[pos]; node >= 0; node = parent_of_node[node]) {
+            int2 rg = range[node];
+            if (rg.y - rg.x + 1 > leaf_size || node == 0) depth++;
+        }
+    }
+    for (int o = 16; o; o >>= 1) depth = max(depth, __shfl_xor_sync(0xffffffffu, depth, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(max_depth, depth);
+    if (pos < n - 1) {
+        int2 rg = range[pos];
+        if (rg.y - rg.x + 1 > leaf_size || pos == 0) atomicAdd(n_emitted, 1);
+    }
+}
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(err, errcap, "lbvh: %s failed: %s", #x, cudaGetErrorString(e_)); return -1; } } while (0)
+
+template <typename T> cudaError_t dalloc(T **p, size_t count) { return cudaMalloc((void **)p, count * sizeof(T) + 16); }
+
+}  // namespace
+
+void lbvh_free(Lbvh *b) {
+    if (!b) return;
+    cudaFree(b->bvh); cudaFree(b->sq0); cudaFree(b->sq1); cudaFree(b->sq2); cudaFree(b->sorted_id);
+    cudaFree(b->range); cudaFree(b->child); cudaFree(b->leaf_lo); cudaFree(b->leaf_hi); cudaFree(b->node_lo); cudaFree(b->node_hi);
+    memset(b, 0, sizeof(*b));
+}
+
+int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
+    // inflate every box by 2^-16 of the largest coordinate magnitude a ray can carry (scene or eye):
+    // covers the rounding slop of the reference's edge tests and of p = P + V*t
+    float eps = ldexpf(fmaxf(reach, b->max_abs), -16);
+    if (!(eps > 0.0f)) eps = 1e-30f;
+    b->reach = fmaxf(reach, b->max_abs);
+    b->eps = eps;
+    if (b->n_tris >= 2) {
+        int n = b->n_tris;
+        k_emit<<<(n - 1 + 255) / 256, 256, 0, st>>>(n, b->leaf_size, eps, (const int2 *)b->range, (const int2 *)b->child,
+                                                   b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, b->bvh);
+        CK(cudaGetLastError());
+        b->launches++;
+    }
+    return 0;
+}
+
+int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, int n, int leaf_size, cudaStream_t st, char *err, size_t errcap) {
+    lbvh_free(b);
+    b->n_tris = n;
+    b->leaf_size = leaf_size < 1 ? 1 : (leaf_size > 8 ? 8 : leaf_size);
+    if (n <= 0) { b->root = ~0; b->n_tris = 0; return 0; }
+    if (n >= (1 << 28)) { snprintf(err, errcap, "lbvh: too many triangles (%d)", n); return -1; }
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, st));
+
+    unsigned *bounds; unsigned long long *keys, *keys2; int *vals, *vals2, *pnode, *pleaf, *arrivals, *stats;
+    CK(dalloc(&bounds, 8)); CK(dalloc(&keys, n)); CK(dalloc(&keys2, n)); CK(dalloc(&vals, n)); CK(dalloc(&vals2, n));
+    CK(dalloc(&pnode, n)); CK(dalloc(&pleaf, n)); CK(dalloc(&arrivals, n)); CK(dalloc(&stats, 4));
+    CK(dalloc(&b->sq0, n)); CK(dalloc(&b->sq1, n)); CK(dalloc(&b->sq2, n)); CK(dalloc(&b->sorted_id, n));
+    CK(dalloc(&b->leaf_lo, n)); CK(dalloc(&b->leaf_hi, n)); CK(dalloc(&b->node_lo, n)); CK(dalloc(&b->node_hi, n));
+    CK(dalloc((int2 **)&b->range, n)); CK(dalloc((int2 **)&b->child, n)); CK(dalloc(&b->bvh, (size_t)4 * n));
+
+    unsigned init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+    CK(cudaMemcpyAsync(bounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    int grid = (n + 255) / 256;
+    k_bounds<<<grid > 1184 ? 1184 : grid, 256, 0, st>>>(q0, q1, q2, n, bounds);
+    k_morton<<<grid, 256, 0, st>>>(q0, q1, q2, n, bounds, keys, vals);
+    b->launches += 2;
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63, st));
+    void *tmp;
+    CK(cudaMalloc(&tmp, tmp_bytes + 16));
+    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63, st));
+    k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, vals2, n, b->sq0, b->sq1, b->sq2, b->leaf_lo, b->leaf_hi);
+    CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    b->launches += 1;
+    CK(cudaMemsetAsync(stats, 0, 16, st));
+    if (n >= 2) {
+        CK(cudaMemsetAsync(arrivals, 0, (size_t)n * sizeof(int), st));
+        k_hierarchy<<<grid, 256, 0, st>>>(keys2, n, (int2 *)b->range, (int2 *)b->child, pnode, pleaf);
+        k_refit<<<grid, 256, 0, st>>>(n, (const int2 *)b->child, pnode, pleaf, b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, arrivals);
+        k_depth<<<grid, 256, 0, st>>>(n, b->leaf_size, (const int2 *)b->range, pnode, pleaf, stats, stats + 1);
+        b->launches += 3;
+    }
+    unsigned hb[8];
+    int hs[4];
+    CK(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hs, stats, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    b->max_abs = ord2f(hb[6]);
+    b->max_depth = hs[0];
+    b->n_nodes = n >= 2 ? hs[1] : 0;
+    b->root = (n <= b->leaf_size || n < 2) ? ~(((0) << 3) | (n - 1)) : 0;
+    if (lbvh_emit(b, 0.0f, st, err, errcap)) return -1;
+    CK(cudaEventRecord(e1, st));
+    CK(cudaEventSynchronize(e1));
+    CK(cudaEventElapsedTime(&b->build_ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
+    cudaFree(pnode); cudaFree(pleaf); cudaFree(arrivals); cudaFree(stats); cudaFree(tmp);
+    CK(cudaGetLastError());
+    return 0;
+}

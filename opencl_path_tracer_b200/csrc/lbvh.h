@@ -1,0 +1,26 @@
+// lbvh.h — host interface of the GPU LBVH builder (lbvh.cu).
+#ifndef PTB_LBVH_H_
+#define PTB_LBVH_H_
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <string.h>
+
+struct Lbvh {
+    // traversal data
+    float4 *bvh;                  // 4 float4 per node
+    float4 *sq0, *sq1, *sq2;      // triangles in Morton order
+    int *sorted_id;               // Morton position → upload index
+    int root;                     // root link
+    // kept for re-emitting with a larger inflation (far-away camera)
+    void *range, *child;          // int2 per internal node
+    float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
+    int n_tris, leaf_size, n_nodes, max_depth;
+    float max_abs, reach, eps, build_ms;
+    unsigned long long launches;
+};
+
+int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, int n, int leaf_size, cudaStream_t st, char *err, size_t errcap);
+// rewrite the traversal nodes with boxes inflated for ray origins up to `reach` from the coordinate origin
+int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap);
+void lbvh_free(Lbvh *b);
+#endif

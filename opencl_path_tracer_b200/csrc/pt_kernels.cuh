@@ -1,0 +1,479 @@
+// pt_kernels.cuh — the path-trace hot path (prog.cl:64-381, 384-389) as hand-written CUDA for
+// sm_100a.  Included by exactly two translation units that differ only in arithmetic flavour
+// (see pt_math.cuh); PT_NS names the namespace the entry points land in.
+//
+// Design (B200-first, not a translation of the OpenCL kernels):
+//   * ONE fused kernel, k_render: camera-ray generation (gen_ray), the bounce loop (trace_ray) and
+//     the running-mean accumulation run in registers for `spp` consecutive samples of a pixel; the
+//     reference's rays[] / rnds[] / colors[] global round trips per bounce (prog.cl:319-379)
+//     become one 4-byte read + 20-byte write per pixel per LAUNCH.
+//   * path regeneration: a lane whose path ended starts its next sample at once, so the warp stays
+//     converged in the intersection loop instead of idling until the longest path of the warp ends.
+//   * warps own 8x4 pixel tiles (coherent primary rays), blocks 16x8.
+//   * closest hit through one of three structures, selected per launch:
+//       BRUTE   all triangles from shared memory (warp-uniform LDS.128 broadcasts)  prog.cl:113-122,318
+//       REFBVH  the host-built per-object trees as uploaded                         prog.cl:123-184
+//       LBVH    the GPU-built Morton LBVH (lbvh.cu), == BRUTE incl. lowest-index tie-break
+//   * the drop-in single-sample kernels of the reference surface (gen_ray → rays[], trace_ray
+//     reading rays[]) are the same code with spp = 1 and from_rays = 1.
+#ifndef PT_NS
+#error "define PT_NS"
+#endif
+
+#include "pt_math.cuh"
+#include "pt_params.h"
+
+namespace PT_NS {
+
+// ---------------------------------------------------------------- small helpers
+PT_DEV float4 ldg4(const float4 *p) { return __ldg(p); }
+
+struct Work {              // per-thread work counters
+    unsigned rays, box, tri, tri1, tri2, tri3, samples;
+};
+
+struct Mat {               // one Material record in registers (prog.cl:1-5)
+    V3 kd, ks, emission, F0;
+    float n, shininess;
+    int type;
+};
+PT_DEV Mat load_material(const RefMaterial *mats, int i) {
+    const float4 *p = reinterpret_cast<const float4 *>(mats + i);
+    float4 a = ldg4(p), b = ldg4(p + 1), c = ldg4(p + 2), d = ldg4(p + 3), e = ldg4(p + 4);
+    Mat m;
+    m.kd = v3(a); m.ks = v3(b); m.emission = v3(c); m.F0 = v3(d);
+    m.n = e.x; m.shininess = e.y; m.type = __float_as_int(e.z);
+    return m;
+}
+
+// ---------------------------------------------------------------- camera (prog.cl:82-92)
+PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2, V3 &P, V3 &D) {
+    int X = (int)cam.XM;
+    int Y = (int)cam.YM;
+    float x = (float)(id % X) + rnd1;
+    float y = (float)(id / X) + rnd2;
+    float sx = pt_div(2.0f * x, (float)X) - 1.0f;
+    float sy = pt_div(2.0f * y, (float)Y) - 1.0f;
+    V3 right = v3(cam.right.x, cam.right.y, cam.right.z) * sx;
+    V3 up = v3(cam.up.x, cam.up.y, cam.up.z) * sy;
+    V3 eye = v3(cam.eye.x, cam.eye.y, cam.eye.z);
+    V3 p = (v3(cam.lookat.x, cam.lookat.y, cam.lookat.z) + right) + up;
+    P = eye;
+    D = normalize(p - eye);
+}
+
+// ---------------------------------------------------------------- ray–triangle (prog.cl:94-112)
+// Returns true and t when the reference's test accepts; the caller applies first_intersect's
+// "t > 0 and strictly closer" rule.  NaN t (dot(V,N)==0) falls through the comparisons like there.
+template <bool COUNT>
+PT_DEV bool triangle_intersect(float4 q0, float4 q1, float4 q2, V3 P, V3 V, float &t_out, Work &wk) {
+    V3 r1 = v3(q0), r2 = v3(q1), r3 = v3(q2), N = v3(q0.w, q1.w, q2.w);
+    if (COUNT) wk.tri++;
+    float t = pt_div(dot(r1 - P, N), dot(V, N));
+    if (t < 0.0f) return false;
+    if (COUNT) wk.tri1++;
+    V3 p = P + V * t;
+    if (dot(cross(r2 - r1, p - r1), N) >= 0.0f) {
+        if (COUNT) wk.tri2++;
+        if (dot(cross(r3 - r2, p - r2), N) >= 0.0f) {
+            if (COUNT) wk.tri3++;
+            if (dot(cross(r1 - r3, p - r3), N) >= 0.0f) {
+                t_out = t;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
+struct Closest {
+    float t;     // -1: none (init_Hit, prog.cl:68-70)
+    int tri;     // index in upload order
+};
+
+// first_intersect over a range held in shared memory (prog.cl:113-122): strict '<' keeps the lowest index on ties
+template <bool COUNT>
+PT_DEV void brute_smem(const float4 *s_tris, int n, V3 P, V3 V, Closest &best, Work &wk) {
+    for (int i = 0; i < n; ++i) {
+        float t;
+        if (triangle_intersect<COUNT>(s_tris[3 * i], s_tris[3 * i + 1], s_tris[3 * i + 2], P, V, t, wk)) {
+            if (t > 0.0f && (best.t < 0.0f || t < best.t)) { best.t = t; best.tri = i; }
+        }
+    }
+}
+template <bool COUNT>
+PT_DEV void brute_global(const SceneDev &sc, int from, int to, V3 P, V3 V, Closest &best, Work &wk) {
+    for (int i = from; i < to; ++i) {
+        float t;
+        if (triangle_intersect<COUNT>(ldg4(sc.q0 + i), ldg4(sc.q1 + i), ldg4(sc.q2 + i), P, V, t, wk)) {
+            if (t > 0.0f && (best.t < 0.0f || t < best.t)) { best.t = t; best.tri = i; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- reference trees (prog.cl:123-184)
+// BBox_intersection with true divisions and OpenCL fmin/fmax NaN rules; kd_intersect's control flow:
+// per object an explicit DFS, left child first, prune on miss / tmax<0 / entry beyond this object's
+// current best (tmin starts at 999999 for every object), best hit kept across objects by strict '<'.
+PT_DEV bool bbox_intersection(const RefNode *node, V3 P, V3 D, float &tmin, float &tmax) {
+    const float4 *p = reinterpret_cast<const float4 *>(node);
+    float4 bl = ldg4(p + 1), tr = ldg4(p + 2);
+    float tx1 = pt_div(bl.x - P.x, D.x), tx2 = pt_div(tr.x - P.x, D.x);
+    tmin = pt_fmin(tx1, tx2);
+    tmax = pt_fmax(tx1, tx2);
+    float ty1 = pt_div(bl.y - P.y, D.y), ty2 = pt_div(tr.y - P.y, D.y);
+    tmin = pt_fmax(tmin, pt_fmin(ty1, ty2));
+    tmax = pt_fmin(tmax, pt_fmax(ty1, ty2));
+    float tz1 = pt_div(bl.z - P.z, D.z), tz2 = pt_div(tr.z - P.z, D.z);
+    tmin = pt_fmax(tmin, pt_fmin(tz1, tz2));
+    tmax = pt_fmin(tmax, pt_fmax(tz1, tz2));
+    return tmax >= tmin;
+}
+template <bool COUNT>
+PT_DEV void refbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &wk) {
+    int stack[64];   // the reference reserves 300 ints; a heap-indexed tree cannot be deeper than 31
+    for (int o = 0; o < sc.n_obj; ++o) {
+        const int shift = __ldg(sc.kd_shift + o);
+        int ptr = 1 + shift;
+        float tmin = 999999.0f;
+        int sp = 0;
+        for (;;) {
+            const RefNode *node = sc.kd_tree + ptr;
+            float dist, tmax;
+            if (COUNT) wk.box++;
+            bool descend = false;
+            if (bbox_intersection(node, P, D, dist, tmax) && tmax >= 0.0f && !(dist > tmin)) {
+                int2 trii = __ldg(reinterpret_cast<const int2 *>(node));
+                if (trii.x < 0) {
+                    if (sp < 64) stack[sp++] = 2 * (ptr - shift) + 1 + shift;
+                    ptr = 2 * (ptr - shift) + shift;
+                    descend = true;
+                } else {
+                    Closest leaf; leaf.t = -1.0f; leaf.tri = -1;
+                    brute_global<COUNT>(sc, trii.x, trii.y, P, D, leaf, wk);
+                    if (leaf.t > 0.0f && (best.t < 0.0f || leaf.t < best.t)) { tmin = leaf.t; best = leaf; }
+                }
+            }
+            if (!descend) {
+                if (sp == 0) break;
+                ptr = stack[--sp];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- GPU LBVH (lbvh.cu)
+// Exactness contract: the result equals brute force over the upload order, i.e. the minimum of
+// (t, index) over all triangles the reference test accepts with t > 0.  Boxes are inflated at
+// build time and the slab interval is widened here, so a box is never culled while it can hold
+// an accepted hit with t <= best.t; equal-t candidates are resolved by index, not visit order.
+// Node = 4 float4 holding both children's boxes (see lbvh.cu); near child first, far child pushed.
+#define PT_LBVH_STACK 64
+PT_DEV float safe_rcp(float d) {
+    // zero (or denormal) direction components: a huge finite reciprocal keeps (lo-P)*inv free of 0*inf NaNs
+    return fabsf(d) > 1e-30f ? 1.0f / d : copysignf(1e30f, d);
+}
+template <bool COUNT>
+PT_DEV void lbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &wk) {
+    const float ix = safe_rcp(D.x), iy = safe_rcp(D.y), iz = safe_rcp(D.z);
+    int stack[PT_LBVH_STACK];
+    int sp = 0;
+    int link = sc.bvh_root;
+    float tbest = 3.0e38f;
+    for (;;) {
+        while (link >= 0) {
+            const float4 *nd = sc.bvh + 4 * (size_t)link;
+            float4 n0 = ldg4(nd), n1 = ldg4(nd + 1), n2 = ldg4(nd + 2), n3 = ldg4(nd + 3);
+            if (COUNT) wk.box += 2;
+            float a, b, l0, l1, r0, r1;
+            a = (n0.x - P.x) * ix; b = (n0.y - P.x) * ix; l0 = fminf(a, b); l1 = fmaxf(a, b);
+            a = (n0.z - P.y) * iy; b = (n0.w - P.y) * iy; l0 = fmaxf(l0, fminf(a, b)); l1 = fminf(l1, fmaxf(a, b));
+            a = (n2.x - P.z) * iz; b = (n2.y - P.z) * iz; l0 = fmaxf(l0, fminf(a, b)); l1 = fminf(l1, fmaxf(a, b));
+            a = (n1.x - P.x) * ix; b = (n1.y - P.x) * ix; r0 = fminf(a, b); r1 = fmaxf(a, b);
+            a = (n1.z - P.y) * iy; b = (n1.w - P.y) * iy; r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
+            a = (n2.z - P.z) * iz; b = (n2.w - P.z) * iz; r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
+            // widen both ends by 8 ulp (each product above carries <= 1.5 ulp)
+            l0 -= fabsf(l0) * 1.0e-6f; l1 += fabsf(l1) * 1.0e-6f;
+            r0 -= fabsf(r0) * 1.0e-6f; r1 += fabsf(r1) * 1.0e-6f;
+            const bool hl = l0 <= l1 && l1 >= 0.0f && l0 <= tbest;
+            const bool hr = r0 <= r1 && r1 >= 0.0f && r0 <= tbest;
+            const int ll = __float_as_int(n3.x), lr = __float_as_int(n3.y);
+            if (hl && hr) {
+                const bool left_first = l0 <= r0;
+                if (sp < PT_LBVH_STACK) stack[sp++] = left_first ? lr : ll;
+                link = left_first ? ll : lr;
+            } else if (hl) {
+                link = ll;
+            } else if (hr) {
+                link = lr;
+            } else {
+                if (sp == 0) return;
+                link = stack[--sp];
+            }
+        }
+        {   // leaf: [first, first+count) in Morton order
+            const int enc = ~link;
+            const int first = enc >> 3, count = (enc & 7) + 1;
+            for (int k = 0; k < count; ++k) {
+                const int pos = first + k;
+                float t;
+                if (triangle_intersect<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk)) {
+                    if (t > 0.0f) {
+                        const int id = __ldg(sc.sorted_id + pos);
+                        if (best.t < 0.0f || t < best.t || (t == best.t && id < best.tri)) {
+                            best.t = t; best.tri = id; tbest = t;
+                        }
+                    }
+                }
+            }
+        }
+        if (sp == 0) return;
+        link = stack[--sp];
+    }
+}
+
+// ---------------------------------------------------------------- bounce sampling (prog.cl:186-245)
+PT_DEV void orthonormal_base(V3 v1, V3 &v2, V3 &v3o) {
+    const float E = 0.001f;
+    if (fabsf(v1.x) <= E && fabsf(v1.z) <= E) {
+        float rl = pt_rcp_sqrt(v1.y * v1.y + v1.z * v1.z);
+        v2 = v3(0.0f, -v1.z * rl, v1.y * rl);
+    } else {
+        float rl = pt_rcp_sqrt(v1.x * v1.x + v1.z * v1.z);
+        v2 = v3(-v1.z * rl, 0.0f, v1.x * rl);
+    }
+    v3o = cross(v1, v2);
+}
+PT_DEV void new_ray_diffuse(V3 hitP, V3 N, float rnd1, float rnd2, V3 &P, V3 &D) {
+    V3 X, Y = N, Z;
+    orthonormal_base(Y, Z, X);
+    float r = pt_sqrt(rnd1);
+    float c, s;
+    pt_disk_angle(rnd2, c, s);
+    float x = r * c, y = r * s, z = pt_sqrt(1.0f - rnd1);
+    D = normalize((X * x + Y * z) + Z * y);
+    P = hitP + Y * 0.001f;
+}
+PT_DEV V3 fresnel(const Mat &m, V3 N, V3 oldD) {
+    float cosa = fabsf(dot(N, oldD));
+    return m.F0 + (1.0f - m.F0) * pt_pow(1.0f - cosa, 5.0f);
+}
+PT_DEV void new_ray_specular(V3 hitP, V3 N, V3 oldD, V3 &P, V3 &D) {
+    float cosa = dot(N, oldD);
+    D = normalize(oldD - (N * cosa) * 2.0f);
+    P = hitP + N * 0.001f;
+}
+
+// per-path throughput state of trace_ray (prog.cl:307-316)
+struct Path {
+    V3 fL, fB, fS, fR, color;
+    bool in;
+};
+PT_DEV void path_reset(Path &p) {
+    p.fL = p.fB = p.fS = p.fR = v3(1.0f, 1.0f, 1.0f);
+    p.color = v3(0.0f, 0.0f, 0.0f);
+    p.in = false;
+}
+
+// One iteration of the bounce loop body after a hit (prog.cl:321-366).  hitN is the stored
+// triangle normal (unflipped).  Updates the ray and the path state.
+PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32_t &rng, Path &ps, V3 eye, int iterations) {
+    if (iterations == 1) ps.color = m.kd + m.emission;                       // flat preview, prog.cl:323-325
+    V3 N = hitN;
+    if (dot(rayD, N) > 0.0f) N = -N;                                        // prog.cl:326-328
+    if (m.type == 0) {                                                      // diffuse + Phong lobe, prog.cl:329-340
+        float r1 = pt_rand(rng), r2 = pt_rand(rng);
+        V3 nP, nD;
+        new_ray_diffuse(hitP, N, r1, r2, nP, nD);
+        float cos_theta = dot(nD, N);
+        ps.fL = ps.fL * (m.kd * pt_fmax(0.0f, cos_theta));
+        if (m.ks.x == 0.0f && m.ks.y == 0.0f && m.ks.z == 0.0f && m.shininess >= 0.0f) {
+            // ks == 0: ks*pow(..) is exactly +0 for any finite pow (its base is in [0,1]), skip the pow
+            ps.fB = ps.fB * v3(0.0f, 0.0f, 0.0f);
+        } else {
+            V3 halfway = normalize(normalize(eye - hitP) + nD);
+            float cos_delta = dot(N, halfway);
+            ps.fB = ps.fB * (m.ks * pt_pow(pt_fmax(0.0f, cos_delta), m.shininess));
+        }
+        rayP = nP; rayD = nD;
+    } else if (m.type == 1) {                                               // mirror, prog.cl:341-345
+        V3 oldD = rayD;
+        new_ray_specular(hitP, N, oldD, rayP, rayD);
+        ps.fS = ps.fS * fresnel(m, N, oldD);
+    } else if (m.type == 2) {                                               // glass, prog.cl:346-357 + 228-245
+        V3 oldD = rayD;
+        bool before = ps.in;
+        float rnd = pt_rand(rng);
+        float n = ps.in ? 1.0f / m.n : m.n;
+        float cosa = dot(-oldD, N);
+        float disc = 1.0f - pt_div(pt_div(1.0f - cosa * cosa, n), n);
+        V3 F = fresnel(m, N, oldD);
+        float prob = ((F.x + F.y) + F.z) / 3.0f;
+        if (disc > 0.0f && rnd > prob) {
+            ps.in = !ps.in;
+            rayP = hitP - N * 0.001f;
+            rayD = normalize(oldD / n + N * (cosa / n - pt_sqrt(disc)));
+        } else {
+            new_ray_specular(hitP, N, oldD, rayP, rayD);
+        }
+        if (before != ps.in) ps.fR = (ps.fR * (1.0f - F)) * (1.0f / (1.0f - prob));
+        else ps.fR = (ps.fR * F) * (1.0f / prob);
+    } else if (m.type == 3) {                                               // emitter, prog.cl:358-366
+        float intensity = pt_fmax(0.0f, dot(-rayD, N));
+        float r1 = pt_rand(rng), r2 = pt_rand(rng);
+        new_ray_diffuse(hitP, N, r1, r2, rayP, rayD);
+        ps.color = ps.color + (((m.emission * (ps.fL + ps.fB)) * ps.fS) * ps.fR) * intensity;
+    }
+    // any other type: ray unchanged, nothing added
+}
+
+// ---------------------------------------------------------------- tone map (prog.cl:247-269)
+PT_DEV float srgb1(float a) { return a <= 0.00304f ? 12.92f * a : 1.055f * pt_pow(a, 0.4167f) - 0.055f; }
+PT_DEV float4 reinhard_tone_map(V3 c) {
+    float L = (0.2126f * c.x + 0.7152f * c.y) + 0.0722f * c.z;
+    float L2 = L / (1.0f + L);
+    c = (c * L2) / L;                     // L == 0 → NaN, as in the reference
+    return make_float4(srgb1(c.x), srgb1(c.y), srgb1(c.z), 1.0f);
+}
+
+// ---------------------------------------------------------------- the fused kernel
+#define PT_BLOCK 128
+#define PT_SMEM_MAX_TRIS 4096   // 192 KB of triangles at most in shared memory
+
+template <int ACCEL, bool COUNT, bool SMEM>
+__global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
+    extern __shared__ float4 s_tris[];
+    const SceneDev &sc = p.sc;
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM) {
+        for (int i = threadIdx.x; i < sc.n_tris; i += PT_BLOCK) {
+            s_tris[3 * i] = ldg4(sc.q0 + i);
+            s_tris[3 * i + 1] = ldg4(sc.q1 + i);
+            s_tris[3 * i + 2] = ldg4(sc.q2 + i);
+        }
+        __syncthreads();
+    }
+    // warp → 8x4 pixel tile, block → 16x8
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    const int id = y * p.W + x;
+    bool mine = x < p.W && y < p.H;
+    if (mine && p.shard_n > 1) mine = ((id / p.shard_group) % p.shard_n) == p.shard_rank;
+    if (mine) {
+        uint32_t rng = (uint32_t)p.rnds[id];
+        V3 acc = v3(0.0f, 0.0f, 0.0f);
+        if (p.sample0 != 0 || p.sum_mode) acc = v3(p.colors[id]);
+        const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
+        const int s_end = p.sample0 + p.spp;
+        int s = p.sample0;
+        int depth = 0;
+        bool alive = false;
+        V3 rayP = eye, rayD = v3(0.0f, 0.0f, 1.0f);
+        Path ps;
+        path_reset(ps);
+        for (;;) {
+            if (!alive) {
+                if (s == s_end) break;
+                if (p.from_rays) {                                   // drop-in trace_ray: gen_ray already ran
+                    const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
+                    rayP = v3(r[0]); rayD = v3(r[1]);
+                } else {                                             // gen_ray fused, prog.cl:384-389
+                    float r1 = pt_rand(rng), r2 = pt_rand(rng);
+                    camera_get_ray(id, p.cam, r1, r2, rayP, rayD);
+                }
+                path_reset(ps);
+                depth = 0;
+                alive = p.iterations > 0;
+            }
+            if (alive) {
+                wk.rays++;
+                Closest best; best.t = -1.0f; best.tri = -1;
+                if (ACCEL == PT_ACCEL_BRUTE) {
+                    if (SMEM) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
+                    else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
+                } else if (ACCEL == PT_ACCEL_REFBVH) {
+                    refbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
+                } else {
+                    lbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
+                }
+                if (best.t > 0.0f) {
+                    // Hit record of triangle_intersect (prog.cl:107): p = P + V*t, N = tri->N, mati
+                    V3 hitP = rayP + rayD * best.t;
+                    V3 hitN = v3(ldg4(sc.q0 + best.tri).w, ldg4(sc.q1 + best.tri).w, ldg4(sc.q2 + best.tri).w);
+                    Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
+                    shade_hit(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
+                    if (++depth == p.iterations) alive = false;
+                } else {
+                    alive = false;                                   // miss: break, prog.cl:367-376
+                }
+            }
+            if (!alive) {                                            // sample finished, prog.cl:379
+                if (p.sum_mode) acc = acc + ps.color;
+                else acc = (acc * (float)s + ps.color) / (float)(s + 1);
+                ++s;
+                wk.samples++;
+            }
+        }
+        p.rnds[id] = (int)rng;
+        p.colors[id] = make_float4(acc.x, acc.y, acc.z, 0.0f);
+        if (p.tex) p.tex[id] = reinhard_tone_map(acc);               // prog.cl:380
+    }
+    // work counters: one atomic per warp and counter
+    if (p.counters) {
+        unsigned v[7] = {wk.rays, wk.box, wk.tri, wk.tri1, wk.tri2, wk.tri3, wk.samples};
+        const int idx[7] = {PT_CNT_RAYS, PT_CNT_BOX, PT_CNT_TRI, PT_CNT_TRI1, PT_CNT_TRI2, PT_CNT_TRI3, PT_CNT_PIXEL_SAMPLES};
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            if (!COUNT && k >= 1 && k <= 5) continue;
+            unsigned long long tot = v[k];
+            for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+            if (lane == 0 && tot) atomicAdd(p.counters + idx[k], tot);
+        }
+    }
+}
+
+// gen_ray as its own launch (prog.cl:384-389): only for hosts that drive the reference's two-kernel sequence
+__global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n) {
+    size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    if (p.shard_n > 1 && (int)((id / (size_t)p.shard_group) % (size_t)p.shard_n) != p.shard_rank) return;
+    uint32_t rng = (uint32_t)p.rnds[id];
+    float r1 = pt_rand(rng), r2 = pt_rand(rng);
+    V3 P, D;
+    camera_get_ray((int)id, p.cam, r1, r2, P, D);
+    p.rnds[id] = (int)rng;
+    float4 *r = reinterpret_cast<float4 *>(p.rays + id);
+    r[0] = make_float4(P.x, P.y, P.z, 0.0f);
+    r[1] = make_float4(D.x, D.y, D.z, 0.0f);
+}
+
+// ---------------------------------------------------------------- host-side dispatch
+template <int ACCEL, bool COUNT, bool SMEM>
+static void launch_one(const RenderParams &p, cudaStream_t st) {
+    dim3 grid((p.W + 15) / 16, (p.H + 7) / 8);
+    size_t smem = (ACCEL == PT_ACCEL_BRUTE && SMEM) ? (size_t)p.sc.n_tris * 3 * sizeof(float4) : 0;
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_render<ACCEL, COUNT, SMEM><<<grid, PT_BLOCK, smem, st>>>(p);
+}
+
+void launch_render(const RenderParams &p, cudaStream_t st) {
+    const bool c = p.count_work != 0;
+    if (p.accel == PT_ACCEL_BRUTE) {
+        const bool smem = p.sc.n_tris <= PT_SMEM_MAX_TRIS;
+        if (smem) { if (c) launch_one<PT_ACCEL_BRUTE, true, true>(p, st); else launch_one<PT_ACCEL_BRUTE, false, true>(p, st); }
+        else      { if (c) launch_one<PT_ACCEL_BRUTE, true, false>(p, st); else launch_one<PT_ACCEL_BRUTE, false, false>(p, st); }
+    } else if (p.accel == PT_ACCEL_REFBVH) {
+        if (c) launch_one<PT_ACCEL_REFBVH, true, false>(p, st); else launch_one<PT_ACCEL_REFBVH, false, false>(p, st);
+    } else {
+        if (c) launch_one<PT_ACCEL_LBVH, true, false>(p, st); else launch_one<PT_ACCEL_LBVH, false, false>(p, st);
+    }
+}
+
+void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t st) {
+    if (n == 0) return;
+    k_gen_ray<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, n);
+}
+
+}  // namespace PT_NS

@@ -1,0 +1,67 @@
+// pt_params.h — launch descriptors shared between the C-ABI (ptb_abi.cu) and the two kernel
+// translation units (pt_kernels_parity.cu / pt_kernels_fast.cu).
+#ifndef PT_PARAMS_H_
+#define PT_PARAMS_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "ptb_types.h"
+
+// closest-hit structure actually used by a launch (PTB_ACCEL_AUTO already resolved)
+enum { PT_ACCEL_BRUTE = 1, PT_ACCEL_REFBVH = 2, PT_ACCEL_LBVH = 3 };
+
+// device counters block (uint64 each)
+enum {
+    PT_CNT_RAYS = 0, PT_CNT_BOX, PT_CNT_TRI, PT_CNT_TRI1, PT_CNT_TRI2, PT_CNT_TRI3, PT_CNT_PIXEL_SAMPLES,
+    PT_CNT_WORDS = 8
+};
+
+// Everything a path kernel reads about the scene.  Passed by value (lives in the constant bank).
+struct SceneDev {
+    // staged triangles in upload order (prog.cl:18-21 → 3 float4 planes, see ptb_types.h)
+    const float4 *q0, *q1, *q2;
+    const uint16_t *mati;
+    int n_tris;
+    const RefMaterial *mats;      // as uploaded (prog.cl:1-5)
+    int n_mats;
+    // the host-built per-object trees exactly as uploaded (prog.cl:27-30, main.cpp:263-303)
+    const RefNode *kd_tree;
+    const int *kd_shift;
+    int n_obj;
+    // GPU-built LBVH (lbvh.cu)
+    const float4 *bvh;            // 2 float4 per node, LbvhNode
+    const float4 *sq0, *sq1, *sq2;// triangles in Morton order
+    const int *sorted_id;         // Morton position → index in upload order
+    int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
+};
+
+struct RenderParams {
+    SceneDev sc;
+    RefCamera cam;                // trace_ray arg 11 / gen_ray arg 1
+    int *rnds;                    // per-pixel RNG state (main.cpp:509,522-526)
+    float4 *colors;               // float3[W*H], 16 B each (main.cpp:520)
+    float4 *tex;                  // RGBA float image or nullptr (main.cpp:512-519)
+    RefRay *rays;                 // gen_ray output / trace_ray input; unused by the fused render
+    int W, H;
+    int iterations;               // trace_ray arg 9
+    int sample0;                  // trace_ray arg 10: index of the first sample of this launch
+    int spp;                      // samples rendered by this launch (1 for the reference's trace_ray)
+    int from_rays;                // 1: first ray of the (single) sample comes from rays[] (drop-in trace_ray)
+    int shard_rank, shard_n, shard_group;   // pixel id selected iff (id / group) % n == rank
+    int sum_mode;                 // 1: colors += sample (spp-split), 0: running mean (prog.cl:379)
+    int accel;                    // PT_ACCEL_*
+    int count_work;               // 1: also count box / triangle tests
+    unsigned long long *counters; // PT_CNT_WORDS words
+};
+
+// one entry per translation unit; implemented in pt_kernels.cuh
+namespace pt_parity {
+void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
+void launch_render(const RenderParams &p, cudaStream_t s);
+}
+namespace pt_fast {
+void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
+void launch_render(const RenderParams &p, cudaStream_t s);
+}
+
+#endif  // PT_PARAMS_H_

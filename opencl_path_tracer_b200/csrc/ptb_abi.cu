@@ -1,0 +1,683 @@
+// ptb_abi.cu — the C-ABI of include/ptb200.h on CUDA (libptb200.so).
+//
+// Replaces the reference host's OpenCL plumbing (main.cpp:389-528, 618-682): buffers are plain
+// device allocations behind ref-counted handles, "kernels" are argument tables for the two entry
+// points of prog.cl, and a launch resolves the arguments into a RenderParams, stages the uploaded
+// triangle records into the SoA float4 layout (once per upload), builds the LBVH (once per upload)
+// and enqueues the fused path kernel on one in-order stream.  There is no CPU path: every entry
+// point that needs the device fails loudly when CUDA is not available.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "lbvh.h"
+#include "pt_params.h"
+#include "ptb200.h"
+#include "resolve.h"
+
+namespace {
+
+struct MemObj {
+    void *dptr = nullptr;
+    size_t bytes = 0;
+    int refs = 1;
+    bool owned = true;
+    bool image = false;
+    int w = 0, h = 0;
+    unsigned long long version = 0;   // bumped by every write: invalidates staged copies
+};
+
+struct Arg {
+    std::vector<unsigned char> value;
+    ptb_mem mem = 0;
+    bool set = false;
+};
+
+struct Staged {                        // device-internal copy of the scene, valid for one upload
+    ptb_mem tris_handle = 0;
+    unsigned long long tris_version = ~0ull;
+    int n_tris = -1;
+    float4 *q0 = nullptr, *q1 = nullptr, *q2 = nullptr;
+    uint16_t *mati = nullptr;
+    int capacity = 0;
+    Lbvh lbvh;
+    bool lbvh_valid = false;
+    int lbvh_leaf = 0;
+};
+
+struct PendingGen {                    // a deferred gen_ray launch (ptb_set_fuse_gen)
+    bool active = false;
+    ptb_mem rays = 0, rnds = 0;
+    RefCamera cam;
+    size_t n = 0;
+};
+
+struct State {
+    bool inited = false;
+    int device = -1;
+    cudaDeviceProp prop;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    std::map<ptb_mem, MemObj> mems;
+    ptb_mem next = 1;
+    Arg args[PTB_KERNEL_COUNT][16];
+    std::string err;
+    int accel = PTB_ACCEL_AUTO, math = PTB_MATH_FAST, pipe = PTB_PIPE_MEGAKERNEL;
+    int fuse_gen = 1;
+    int shard_rank = 0, shard_n = 1, shard_group = 1;
+    int sum_mode = 0, count_work = 0;
+    int lbvh_leaf = 4;
+    int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
+    unsigned long long *counters = nullptr;
+    unsigned long long launches = 0;
+    Staged staged;
+    PendingGen pending;
+};
+// immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
+// during static destruction, after which ptb_release still gets called
+State &G = *new State();
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (G.err.empty()) {
+        G.err = buf;
+        fprintf(stderr, "ptb(cuda): %s\n", buf);
+    }
+    return code;
+}
+#define CUDA_OK(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return fail(PTB_ERR_DEVICE, "%s: %s", #call, cudaGetErrorString(e_));   \
+    } while (0)
+#define NEED_INIT()                                            \
+    do {                                                       \
+        if (!G.inited) { int rc_ = ptb_init(-1); if (rc_) return rc_; } \
+        if (!G.err.empty()) return PTB_ERR_DEVICE;             \
+    } while (0)
+
+MemObj *find(ptb_mem h) {
+    auto it = G.mems.find(h);
+    return it == G.mems.end() ? nullptr : &it->second;
+}
+
+template <typename T> T arg_val(int k, int i, bool *ok) {
+    T v;
+    memset(&v, 0, sizeof v);
+    const Arg &a = G.args[k][i];
+    if (a.set && a.value.size() >= sizeof(T)) memcpy(&v, a.value.data(), sizeof(T));
+    else if (ok) *ok = false;
+    return v;
+}
+MemObj *arg_mem(int k, int i) { return G.args[k][i].set ? find(G.args[k][i].mem) : nullptr; }
+
+// ---------------------------------------------------------------- staging (AoS upload → SoA planes)
+__global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 *q1, float4 *q2, uint16_t *mati) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 *t = reinterpret_cast<const float4 *>(tris + i);   // 5 x 16 B per record
+    float4 r1 = t[0], r2 = t[1], r3 = t[2], N = t[3];
+    q0[i] = make_float4(r1.x, r1.y, r1.z, N.x);
+    q1[i] = make_float4(r2.x, r2.y, r2.z, N.y);
+    q2[i] = make_float4(r3.x, r3.y, r3.z, N.z);
+    mati[i] = tris[i].mati;
+}
+
+int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
+    Staged &s = G.staged;
+    if (s.tris_handle == handle && s.tris_version == tris->version && s.n_tris == n_tris) return PTB_SUCCESS;
+    if ((size_t)n_tris * sizeof(RefTriangle) > tris->bytes)
+        return fail(PTB_ERR_INVALID_ARGS, "trace_ray: tris_size %d exceeds the triangle buffer (%zu bytes)", n_tris, tris->bytes);
+    if (n_tris > s.capacity) {
+        cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.mati);
+        s.capacity = 0;
+        size_t cap = (size_t)n_tris + 16;
+        CUDA_OK(cudaMalloc((void **)&s.q0, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.q1, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.q2, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.mati, cap * sizeof(uint16_t)));
+        s.capacity = n_tris;
+    }
+    if (n_tris > 0) {
+        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.mati);
+        CUDA_OK(cudaGetLastError());
+        G.launches++;
+    }
+    s.tris_handle = handle;
+    s.tris_version = tris->version;
+    s.n_tris = n_tris;
+    s.lbvh_valid = false;
+    return PTB_SUCCESS;
+}
+
+int resolve_accel(int n_tris, bool have_tree) {
+    if (G.accel == PTB_ACCEL_BRUTE) return PT_ACCEL_BRUTE;
+    if (G.accel == PTB_ACCEL_REFBVH) return have_tree ? PT_ACCEL_REFBVH : PT_ACCEL_BRUTE;
+    if (G.accel == PTB_ACCEL_LBVH) return n_tris > 0 ? PT_ACCEL_LBVH : PT_ACCEL_BRUTE;
+    return n_tris <= G.brute_max ? PT_ACCEL_BRUTE : PT_ACCEL_LBVH;
+}
+
+int ensure_lbvh(float reach) {
+    Staged &s = G.staged;
+    char err[256];
+    err[0] = 0;
+    if (!s.lbvh_valid || s.lbvh_leaf != G.lbvh_leaf) {
+        unsigned long long before = s.lbvh.launches;
+        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.n_tris, G.lbvh_leaf, G.stream, err, sizeof err))
+            return fail(PTB_ERR_DEVICE, "%s", err);
+        G.launches += s.lbvh.launches - before + 4;   // + the radix-sort passes
+        s.lbvh_valid = true;
+        s.lbvh_leaf = G.lbvh_leaf;
+        if (s.lbvh.max_depth > 62)
+            return fail(PTB_ERR_DEVICE, "lbvh: tree depth %d exceeds the traversal stack", s.lbvh.max_depth);
+    }
+    if (reach > 4.0f * s.lbvh.reach) {   // camera far outside the scene: widen the boxes (cheap re-emit)
+        if (lbvh_emit(&s.lbvh, reach, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+        G.launches++;
+    }
+    return PTB_SUCCESS;
+}
+
+// Build the launch descriptor from the trace_ray argument table (prog.cl:292-304 ↔ main.cpp:648-660)
+int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
+    const int K = PTB_KERNEL_TRACE_RAY;
+    memset(&p, 0, sizeof p);
+    MemObj *tex = arg_mem(K, 0), *tris = arg_mem(K, 1), *mats = arg_mem(K, 3), *tree = arg_mem(K, 4), *shift = arg_mem(K, 5),
+           *rays = arg_mem(K, 7), *rnds = arg_mem(K, 8), *colors = arg_mem(K, 12);
+    bool ok = true;
+    int tris_size = arg_val<int>(K, 2, &ok);
+    int shift_size = arg_val<int>(K, 6, &ok);
+    p.iterations = arg_val<int>(K, 9, &ok);
+    p.sample0 = arg_val<int>(K, 10, &ok);
+    p.cam = arg_val<RefCamera>(K, 11, &ok);
+    if (!ok) return fail(PTB_ERR_INVALID_ARGS, "trace_ray: a by-value argument (2, 6, 9, 10 or 11) is not set");
+    if (!tris || !mats || !rnds || !colors) return fail(PTB_ERR_INVALID_ARGS, "trace_ray: buffer argument 1, 3, 8 or 12 is not set");
+    if (from_rays && !rays) return fail(PTB_ERR_INVALID_ARGS, "trace_ray: rays (argument 7) is not set");
+    size_t npix = W * H;
+    if (npix == 0 || W > 65535u * 16u || H > 65535u * 8u) return fail(PTB_ERR_INVALID_VALUE, "trace_ray: bad launch size %zux%zu", W, H);
+    if (rnds->bytes < npix * 4 || colors->bytes < npix * 16 || (from_rays && rays->bytes < npix * 32))
+        return fail(PTB_ERR_INVALID_ARGS, "trace_ray: rnds/colors/rays smaller than the %zux%zu launch", W, H);
+    if (tex && tex->bytes < npix * 16) tex = nullptr;
+    if (tris_size < 0) tris_size = 0;
+    int rc = stage_scene(tris, G.args[K][1].mem, tris_size);
+    if (rc) return rc;
+    Staged &s = G.staged;
+    bool have_tree = tree && shift && shift_size > 0 && shift->bytes >= (size_t)shift_size * 4;
+    p.accel = resolve_accel(tris_size, have_tree);
+    p.sc.q0 = s.q0; p.sc.q1 = s.q1; p.sc.q2 = s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
+    p.sc.mats = (const RefMaterial *)mats->dptr;
+    p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
+    if (have_tree) {
+        p.sc.kd_tree = (const RefNode *)tree->dptr;
+        p.sc.kd_shift = (const int *)shift->dptr;
+        p.sc.n_obj = shift_size;
+    }
+    if (p.accel == PT_ACCEL_LBVH) {
+        float reach = fmaxf(fabsf(p.cam.eye.x), fmaxf(fabsf(p.cam.eye.y), fabsf(p.cam.eye.z)));
+        rc = ensure_lbvh(reach);
+        if (rc) return rc;
+        p.sc.bvh = s.lbvh.bvh; p.sc.sq0 = s.lbvh.sq0; p.sc.sq1 = s.lbvh.sq1; p.sc.sq2 = s.lbvh.sq2;
+        p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
+    }
+    p.rnds = (int *)rnds->dptr;
+    p.colors = (float4 *)colors->dptr;
+    p.tex = tex ? (float4 *)tex->dptr : nullptr;
+    p.rays = rays ? (RefRay *)rays->dptr : nullptr;
+    p.W = (int)W; p.H = (int)H;
+    p.spp = spp;
+    p.from_rays = from_rays ? 1 : 0;
+    p.shard_rank = G.shard_rank; p.shard_n = G.shard_n; p.shard_group = G.shard_group;
+    p.sum_mode = G.sum_mode;
+    p.count_work = G.count_work;
+    p.counters = G.counters;
+    return PTB_SUCCESS;
+}
+
+int run_gen_ray(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n) {
+    MemObj *rays = find(rays_h), *rnds = find(rnds_h);
+    if (!rays || !rnds) return fail(PTB_ERR_INVALID_ARGS, "gen_ray: buffer argument 0 or 2 is not set");
+    if (rays->bytes < n * 32 || rnds->bytes < n * 4) return fail(PTB_ERR_INVALID_ARGS, "gen_ray: rays/rnds smaller than the launch (%zu)", n);
+    RenderParams p;
+    memset(&p, 0, sizeof p);
+    p.cam = cam;
+    p.rays = (RefRay *)rays->dptr;
+    p.rnds = (int *)rnds->dptr;
+    p.shard_rank = G.shard_rank; p.shard_n = G.shard_n; p.shard_group = G.shard_group;
+    if (G.math == PTB_MATH_PARITY) pt_parity::launch_gen_ray(p, n, G.stream);
+    else pt_fast::launch_gen_ray(p, n, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches++;
+    return PTB_SUCCESS;
+}
+
+int flush_pending() {
+    if (!G.pending.active) return PTB_SUCCESS;
+    G.pending.active = false;
+    return run_gen_ray(G.pending.rays, G.pending.rnds, G.pending.cam, G.pending.n);
+}
+
+int run_render(const RenderParams &p) {
+    if (G.math == PTB_MATH_PARITY) pt_parity::launch_render(p, G.stream);
+    else pt_fast::launch_render(p, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches++;
+    return PTB_SUCCESS;
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------- bring-up
+int ptb_init(int device_ordinal) {
+    if (G.inited) return G.err.empty() ? PTB_SUCCESS : PTB_ERR_DEVICE;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(PTB_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU fallback", e == cudaSuccess ? "count = 0" : cudaGetErrorString(e));
+    int dev = device_ordinal;
+    if (dev < 0) {
+        const char *lr = getenv("LOCAL_RANK");
+        dev = lr ? atoi(lr) % count : 0;
+    }
+    if (dev >= count) return fail(PTB_ERR_NO_DEVICE, "device %d requested, %d present", dev, count);
+    CUDA_OK(cudaSetDevice(dev));
+    CUDA_OK(cudaGetDeviceProperties(&G.prop, dev));
+    CUDA_OK(cudaStreamCreateWithFlags(&G.own_stream, cudaStreamNonBlocking));
+    G.stream = G.own_stream;
+    CUDA_OK(cudaMalloc((void **)&G.counters, PT_CNT_WORDS * sizeof(unsigned long long)));
+    CUDA_OK(cudaMemset(G.counters, 0, PT_CNT_WORDS * sizeof(unsigned long long)));
+    G.device = dev;
+    G.inited = true;
+    const char *env;
+    if ((env = getenv("PTB_MATH"))) G.math = atoi(env) ? PTB_MATH_FAST : PTB_MATH_PARITY;
+    if ((env = getenv("PTB_ACCEL"))) G.accel = atoi(env);
+    if ((env = getenv("PTB_LBVH_LEAF"))) G.lbvh_leaf = atoi(env);
+    if ((env = getenv("PTB_BRUTE_MAX"))) G.brute_max = atoi(env);
+    return PTB_SUCCESS;
+}
+
+int ptb_shutdown(void) {
+    if (!G.inited) return PTB_SUCCESS;
+    cudaSetDevice(G.device);
+    cudaStreamSynchronize(G.stream);
+    for (auto &kv : G.mems)
+        if (kv.second.owned) cudaFree(kv.second.dptr);
+    G.mems.clear();
+    Staged &s = G.staged;
+    cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.mati);
+    lbvh_free(&s.lbvh);
+    s = Staged();
+    cudaFree(G.counters);
+    G.counters = nullptr;
+    cudaStreamDestroy(G.own_stream);
+    G.own_stream = G.stream = nullptr;
+    for (auto &k : G.args) for (auto &a : k) a = Arg();
+    G.pending.active = false;
+    G.inited = false;
+    return PTB_SUCCESS;
+}
+
+int ptb_device_string(int what, char *dst, size_t cap) {
+    if (!dst || !cap) return PTB_ERR_INVALID_VALUE;
+    NEED_INIT();
+    int drv = 0, rt = 0;
+    cudaDriverGetVersion(&drv);
+    cudaRuntimeGetVersion(&rt);
+    switch (what) {
+        case 0: snprintf(dst, cap, "%s", G.prop.name); break;
+        case 1: snprintf(dst, cap, "CUDA sm_%d%d, %d SMs, %.1f GB", G.prop.major, G.prop.minor, G.prop.multiProcessorCount, G.prop.totalGlobalMem / 1e9); break;
+        case 2: snprintf(dst, cap, "driver %d.%d / runtime %d.%d", drv / 1000, (drv % 100) / 10, rt / 1000, (rt % 100) / 10); break;
+        case 3: snprintf(dst, cap, "prebuilt CUDA kernels for sm_100a (prog.cl is not JIT-compiled)"); break;
+        default: snprintf(dst, cap, "ptb_render ptb_lbvh ptb_pixel_shard ptb_sum_accumulate"); break;
+    }
+    return PTB_SUCCESS;
+}
+int ptb_device_compute_units(void) {
+    if (!G.inited && ptb_init(-1)) return 0;
+    return G.prop.multiProcessorCount;
+}
+const char *ptb_backend_name(void) { return "cuda-sm100a"; }
+
+// ---------------------------------------------------------------- memory
+ptb_mem ptb_alloc(size_t bytes) {
+    if (!G.inited && ptb_init(-1)) return 0;
+    if (!G.err.empty()) return 0;
+    MemObj m;
+    m.bytes = bytes;
+    cudaError_t e = cudaMalloc(&m.dptr, bytes ? bytes : 1);
+    if (e != cudaSuccess) { fail(PTB_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); return 0; }
+    cudaMemsetAsync(m.dptr, 0, bytes, G.stream);
+    ptb_mem h = G.next++;
+    G.mems[h] = m;
+    return h;
+}
+ptb_mem ptb_alloc_image(int w, int h) {
+    if (w <= 0 || h <= 0) { fail(PTB_ERR_INVALID_VALUE, "ptb_alloc_image: bad extent %dx%d", w, h); return 0; }
+    ptb_mem hd = ptb_alloc((size_t)w * (size_t)h * sizeof(float4));
+    MemObj *m = find(hd);
+    if (m) { m->image = true; m->w = w; m->h = h; }
+    return hd;
+}
+int ptb_retain(ptb_mem h) {
+    MemObj *m = find(h);
+    if (!m) return PTB_ERR_INVALID_MEM;
+    m->refs++;
+    return PTB_SUCCESS;
+}
+int ptb_release(ptb_mem h) {
+    MemObj *m = find(h);
+    if (!m) return PTB_ERR_INVALID_MEM;
+    if (--m->refs == 0) {
+        if (G.inited) {
+            if (G.pending.active && (G.pending.rays == h || G.pending.rnds == h)) G.pending.active = false;
+            if (m->owned) { cudaStreamSynchronize(G.stream); cudaFree(m->dptr); }
+        }
+        if (G.staged.tris_handle == h) G.staged.tris_handle = 0;
+        G.mems.erase(h);
+    }
+    return PTB_SUCCESS;
+}
+int ptb_write(ptb_mem h, size_t off, size_t bytes, const void *src) {
+    NEED_INIT();
+    MemObj *m = find(h);
+    if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_write: bad handle");
+    if (bytes == 0) return PTB_SUCCESS;
+    if (!src || off + bytes > m->bytes) return fail(PTB_ERR_INVALID_VALUE, "ptb_write: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
+    int rc = flush_pending();
+    if (rc) return rc;
+    CUDA_OK(cudaMemcpyAsync((char *)m->dptr + off, src, bytes, cudaMemcpyHostToDevice, G.stream));
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    m->version++;
+    return PTB_SUCCESS;
+}
+int ptb_read(ptb_mem h, size_t off, size_t bytes, void *dst) {
+    NEED_INIT();
+    MemObj *m = find(h);
+    if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_read: bad handle");
+    if (bytes == 0) return PTB_SUCCESS;
+    if (!dst || off + bytes > m->bytes) return fail(PTB_ERR_INVALID_VALUE, "ptb_read: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
+    int rc = flush_pending();
+    if (rc) return rc;
+    CUDA_OK(cudaMemcpyAsync(dst, (const char *)m->dptr + off, bytes, cudaMemcpyDeviceToHost, G.stream));
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    return PTB_SUCCESS;
+}
+size_t ptb_mem_size(ptb_mem h) {
+    MemObj *m = find(h);
+    return m ? m->bytes : 0;
+}
+ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes) {
+    if (!G.inited && ptb_init(-1)) return 0;
+    if (!device_ptr) return 0;
+    MemObj m;
+    m.dptr = device_ptr;
+    m.bytes = bytes;
+    m.owned = false;
+    ptb_mem h = G.next++;
+    G.mems[h] = m;
+    return h;
+}
+void *ptb_device_ptr(ptb_mem h) {
+    MemObj *m = find(h);
+    if (!m) return nullptr;
+    flush_pending();
+    m->version++;   // the caller may write through the pointer
+    return m->dptr;
+}
+
+// ---------------------------------------------------------------- kernels
+int ptb_kernel_id(const char *name) {
+    if (!name) return PTB_ERR_INVALID_KERNEL;
+    if (!strcmp(name, "gen_ray")) return PTB_KERNEL_GEN_RAY;
+    if (!strcmp(name, "trace_ray")) return PTB_KERNEL_TRACE_RAY;
+    if (!strcmp(name, "filt_im")) return PTB_KERNEL_FILT_IM;
+    return PTB_ERR_INVALID_KERNEL;
+}
+int ptb_set_arg(int k, int i, size_t bytes, const void *value) {
+    if (k < 0 || k >= PTB_KERNEL_COUNT || i < 0 || i >= 16 || !value) return fail(PTB_ERR_INVALID_VALUE, "ptb_set_arg(%d,%d): bad kernel or index", k, i);
+    Arg &a = G.args[k][i];
+    a.value.assign((const unsigned char *)value, (const unsigned char *)value + bytes);
+    a.mem = 0;
+    a.set = true;
+    return PTB_SUCCESS;
+}
+int ptb_set_arg_mem(int k, int i, ptb_mem m) {
+    if (k < 0 || k >= PTB_KERNEL_COUNT || i < 0 || i >= 16) return fail(PTB_ERR_INVALID_VALUE, "ptb_set_arg_mem(%d,%d): bad kernel or index", k, i);
+    Arg &a = G.args[k][i];
+    a.value.clear();
+    a.mem = m;
+    a.set = true;
+    return PTB_SUCCESS;
+}
+
+int ptb_launch(int k, size_t gx, size_t gy) {
+    NEED_INIT();
+    if (gy == 0) gy = 1;
+    if (k == PTB_KERNEL_GEN_RAY) {
+        // gen_ray(rays, Camera, rnds) — prog.cl:384-386 ↔ main.cpp:638-640, 1-D over W*H (main.cpp:642)
+        int rc = flush_pending();
+        if (rc) return rc;
+        bool ok = true;
+        RefCamera cam = arg_val<RefCamera>(k, 1, &ok);
+        if (!ok || !G.args[k][0].set || !G.args[k][2].set) return fail(PTB_ERR_INVALID_ARGS, "gen_ray: arguments 0..2 must be set");
+        size_t n = gx * gy;
+        if (G.fuse_gen) {
+            G.pending.active = true;
+            G.pending.rays = G.args[k][0].mem;
+            G.pending.rnds = G.args[k][2].mem;
+            G.pending.cam = cam;
+            G.pending.n = n;
+            return PTB_SUCCESS;
+        }
+        return run_gen_ray(G.args[k][0].mem, G.args[k][2].mem, cam, n);
+    }
+    if (k == PTB_KERNEL_TRACE_RAY) {
+        const int K = PTB_KERNEL_TRACE_RAY;
+        bool fused = false;
+        if (G.pending.active) {
+            bool ok = true;
+            RefCamera cam = arg_val<RefCamera>(K, 11, &ok);
+            fused = ok && G.pending.rays == G.args[K][7].mem && G.pending.rnds == G.args[K][8].mem && G.pending.n == gx * gy &&
+                    memcmp(&cam, &G.pending.cam, 72) == 0 && (int)cam.XM == (int)gx;
+            if (fused) G.pending.active = false;
+            else { int rc = flush_pending(); if (rc) return rc; }
+        }
+        RenderParams p;
+        int rc = make_params(p, gx, gy, 1, !fused);
+        if (rc) return rc;
+        return run_render(p);
+    }
+    if (k == PTB_KERNEL_FILT_IM) {
+        // filt_im(tex, colors) — prog.cl:391-427; launched over (W,H) (main.cpp:665-668, commented out there)
+        int rc = flush_pending();
+        if (rc) return rc;
+        return ptb_filter_median(G.args[k][1].mem, G.args[k][0].mem, (int)gx, (int)gy);
+    }
+    return fail(PTB_ERR_INVALID_KERNEL, "ptb_launch: unknown kernel id %d", k);
+}
+
+int ptb_finish(void) {
+    NEED_INIT();
+    int rc = flush_pending();
+    if (rc) return rc;
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    return PTB_SUCCESS;
+}
+const char *ptb_last_error(void) { return G.err.c_str(); }
+void ptb_clear_error(void) { G.err.clear(); }
+
+// ---------------------------------------------------------------- extensions
+int ptb_set_accel(int accel) {
+    if (accel < PTB_ACCEL_AUTO || accel > PTB_ACCEL_LBVH) return PTB_ERR_INVALID_VALUE;
+    G.accel = accel;
+    return PTB_SUCCESS;
+}
+int ptb_set_math(int math) {
+    if (math != PTB_MATH_PARITY && math != PTB_MATH_FAST) return PTB_ERR_INVALID_VALUE;
+    G.math = math;
+    return PTB_SUCCESS;
+}
+int ptb_set_pipeline(int pipe) {
+    if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT) return PTB_ERR_INVALID_VALUE;
+    G.pipe = pipe;
+    return PTB_SUCCESS;
+}
+int ptb_set_fuse_gen(int on) {
+    int rc = G.inited ? flush_pending() : PTB_SUCCESS;
+    G.fuse_gen = on ? 1 : 0;
+    return rc;
+}
+int ptb_set_lbvh_leaf(int max_tris) {
+    if (max_tris < 1 || max_tris > 8) return PTB_ERR_INVALID_VALUE;
+    G.lbvh_leaf = max_tris;
+    return PTB_SUCCESS;
+}
+int ptb_get_accel(void) {
+    const int K = PTB_KERNEL_TRACE_RAY;
+    bool ok = true;
+    int n = arg_val<int>(K, 2, &ok);
+    int ns = arg_val<int>(K, 6, &ok);
+    int a = resolve_accel(ok ? n : 0, arg_mem(K, 4) && arg_mem(K, 5) && ns > 0);
+    return a == PT_ACCEL_BRUTE ? PTB_ACCEL_BRUTE : a == PT_ACCEL_REFBVH ? PTB_ACCEL_REFBVH : PTB_ACCEL_LBVH;
+}
+int ptb_build_accel(void) {
+    NEED_INIT();
+    const int K = PTB_KERNEL_TRACE_RAY;
+    MemObj *tris = arg_mem(K, 1);
+    bool ok = true;
+    int n = arg_val<int>(K, 2, &ok);
+    if (!tris || !ok) return PTB_SUCCESS;   // nothing uploaded yet: the first launch will build
+    int rc = stage_scene(tris, G.args[K][1].mem, n < 0 ? 0 : n);
+    if (rc) return rc;
+    int ns = arg_val<int>(K, 6, &ok);
+    if (resolve_accel(n, arg_mem(K, 4) && arg_mem(K, 5) && ns > 0) == PT_ACCEL_LBVH) {
+        rc = ensure_lbvh(0.0f);
+        if (rc) return rc;
+    }
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    return PTB_SUCCESS;
+}
+
+int ptb_render(int spp) {
+    NEED_INIT();
+    if (spp <= 0) return PTB_SUCCESS;
+    int rc = flush_pending();
+    if (rc) return rc;
+    bool ok = true;
+    RefCamera cam = arg_val<RefCamera>(PTB_KERNEL_TRACE_RAY, 11, &ok);
+    if (!ok) return fail(PTB_ERR_INVALID_ARGS, "ptb_render: trace_ray argument 11 (Camera) is not set");
+    RenderParams p;
+    rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
+    if (rc) return rc;
+    return run_render(p);
+}
+
+int ptb_set_pixel_shard(int rank, int n, int group) {
+    if (n < 1 || rank < 0 || rank >= n || group < 1) return PTB_ERR_INVALID_VALUE;
+    int rc = G.inited ? flush_pending() : PTB_SUCCESS;
+    G.shard_rank = rank; G.shard_n = n; G.shard_group = group;
+    return rc;
+}
+int ptb_set_accumulate_sum(int on) {
+    G.sum_mode = on ? 1 : 0;
+    return PTB_SUCCESS;
+}
+int ptb_resolve_sum(ptb_mem colors_sum, int total_spp) {
+    NEED_INIT();
+    MemObj *m = find(colors_sum);
+    if (!m || total_spp <= 0) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_sum: bad buffer or sample count");
+    int rc = flush_pending();
+    if (rc) return rc;
+    resolve_scale((float4 *)m->dptr, m->bytes / sizeof(float4), 1.0f / (float)total_spp, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches++;
+    m->version++;
+    return PTB_SUCCESS;
+}
+
+int ptb_set_count_work(int on) {
+    G.count_work = on ? 1 : 0;
+    return PTB_SUCCESS;
+}
+int ptb_get_counters(ptb_counters *out) {
+    NEED_INIT();
+    if (!out) return PTB_ERR_INVALID_VALUE;
+    int rc = flush_pending();
+    if (rc) return rc;
+    unsigned long long h[PT_CNT_WORDS];
+    CUDA_OK(cudaMemcpyAsync(h, G.counters, sizeof h, cudaMemcpyDeviceToHost, G.stream));
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    out->rays = h[PT_CNT_RAYS]; out->box_tests = h[PT_CNT_BOX]; out->tri_tests = h[PT_CNT_TRI];
+    out->tri_stage1 = h[PT_CNT_TRI1]; out->tri_stage2 = h[PT_CNT_TRI2]; out->tri_stage3 = h[PT_CNT_TRI3];
+    out->pixel_samples = h[PT_CNT_PIXEL_SAMPLES];
+    return PTB_SUCCESS;
+}
+int ptb_reset_counters(void) {
+    NEED_INIT();
+    CUDA_OK(cudaMemsetAsync(G.counters, 0, PT_CNT_WORDS * sizeof(unsigned long long), G.stream));
+    return PTB_SUCCESS;
+}
+
+int ptb_resolve_rgba8(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host) {
+    NEED_INIT();
+    MemObj *m = find(colors);
+    size_t n = (size_t)width * (size_t)height;
+    if (!m || !dst_host || width <= 0 || height <= 0 || m->bytes < n * 16) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_rgba8: bad arguments");
+    int rc = flush_pending();
+    if (rc) return rc;
+    unsigned char *d;
+    CUDA_OK(cudaMalloc((void **)&d, n * 4));
+    resolve_rgba8((const float4 *)m->dptr, width, height, mode, d, G.stream);
+    G.launches++;
+    cudaError_t e = cudaMemcpyAsync(dst_host, d, n * 4, cudaMemcpyDeviceToHost, G.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_resolve_rgba8: %s", cudaGetErrorString(e));
+    return PTB_SUCCESS;
+}
+int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height) {
+    NEED_INIT();
+    MemObj *c = find(colors), *im = find(image);
+    size_t n = (size_t)width * (size_t)height;
+    if (!c || !im || width <= 0 || height <= 0 || c->bytes < n * 16 || im->bytes < n * 16)
+        return fail(PTB_ERR_INVALID_VALUE, "ptb_filter_median: bad arguments");
+    int rc = flush_pending();
+    if (rc) return rc;
+    filter_median((const float4 *)c->dptr, (float4 *)im->dptr, width, height, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches++;
+    im->version++;
+    return PTB_SUCCESS;
+}
+
+int ptb_set_stream(void *cuda_stream) {
+    NEED_INIT();
+    int rc = flush_pending();
+    if (rc) return rc;
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    G.stream = cuda_stream ? (cudaStream_t)cuda_stream : G.own_stream;
+    return PTB_SUCCESS;
+}
+void *ptb_get_stream(void) { return (void *)G.stream; }
+int ptb_accel_stats(int *n_nodes, int *n_tris, int *max_depth, float *build_ms) {
+    const Lbvh &b = G.staged.lbvh;
+    bool v = G.staged.lbvh_valid;
+    if (n_nodes) *n_nodes = v ? b.n_nodes : 0;
+    if (n_tris) *n_tris = v ? b.n_tris : 0;
+    if (max_depth) *max_depth = v ? b.max_depth : 0;
+    if (build_ms) *build_ms = v ? b.build_ms : 0.0f;
+    return PTB_SUCCESS;
+}
+uint64_t ptb_launch_count(void) { return G.launches; }
+
+}  // extern "C"

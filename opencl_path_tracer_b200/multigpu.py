@@ -1,0 +1,76 @@
+"""Multi-GPU drivers: one process per GPU, torch.distributed for the plumbing.
+
+The path shards naturally (pixels and samples are independent, the scene is read-only), so there is
+exactly one exchange step per render:
+
+* **spp-split** — every rank renders ``spp`` samples of EVERY pixel into a per-pixel SUM buffer with its
+  own seed set (rank r takes outputs ``[r*W*H, (r+1)*W*H)`` of the host's ``minstd_rand0`` sequence, so
+  rank 0 alone reproduces the reference's seeds), then one ``reduce(SUM)`` of the float buffer to rank 0
+  over NCCL/NVLink and a ``sum / total_spp`` resolve.  Not stream-identical to a 1-GPU render of
+  ``N*spp`` samples (different random numbers), validated by converged-image RMSE.
+* **tile-split** — rank r renders the pixel groups ``(id // group) % N == r`` for ALL samples with the
+  reference's per-pixel seeds, then the disjoint pixel sets are summed (every pixel is non-zero on
+  exactly one rank) — bitwise identical to the 1-GPU image.
+
+The collective runs on whatever backend the process group has (NCCL on the GPU box, gloo in the CPU
+tests); only the render call needs the CUDA library.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def rank_seed_skip(rank, width, height):
+    """Offset into the host generator's output sequence for ``rank`` (main.cpp:522-526 continues)."""
+    return rank * width * height
+
+
+def shard_group(width, rows=8):
+    """Pixel-group size of the tile split: bands of ``rows`` scanlines (matches the kernel's 16x8 blocks)."""
+    return width * rows
+
+
+def pixel_owner(width, height, nranks, group):
+    """(H*W,) array: which rank renders which pixel id under ptb_set_pixel_shard(rank, nranks, group)."""
+    ids = np.arange(width * height, dtype=np.int64)
+    return ((ids // group) % nranks).astype(np.int32)
+
+
+def reduce_sum_to_root(buf, group=None):
+    """The one collective of the spp-split: SUM of the per-rank accumulation buffers at rank 0."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM, group=group)
+    return buf
+
+
+def merge_spp_split(sum_buf, total_spp):
+    """sum → mean on the root (the CUDA path uses ptb_resolve_sum; this is the host-side statement of it)."""
+    return sum_buf / float(total_spp)
+
+
+def merge_tile_split(local_colors, group=None):
+    """Disjoint pixel sets: a SUM all-reduce is an exact gather (x + 0 == x for every finite x, and the
+    non-owned pixels are exactly +0)."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(local_colors, op=dist.ReduceOp.SUM, group=group)
+    return local_colors
+
+
+class DeviceFrame:
+    """colors / rnds / image buffers as torch CUDA tensors wrapped into ptb handles, so the same memory is
+    visible to the path kernel (through the C-ABI) and to NCCL (through torch.distributed)."""
+
+    def __init__(self, ptb, width, height, device):
+        self.ptb, self.W, self.H = ptb, width, height
+        n = width * height
+        self.colors = torch.zeros(n, 4, dtype=torch.float32, device=device)
+        self.rnds = torch.zeros(n, dtype=torch.int32, device=device)
+        self.image = torch.zeros(n, 4, dtype=torch.float32, device=device)
+        self.h_colors = ptb.wrap_device(self.colors.data_ptr(), n * 16)
+        self.h_rnds = ptb.wrap_device(self.rnds.data_ptr(), n * 4)
+        self.h_image = ptb.wrap_device(self.image.data_ptr(), n * 16)
+
+    def attach(self, scene):
+        """Point a host.Scene at these buffers instead of its own."""
+        scene.buffer_colors, scene.buffer_rnds, scene.cl_screen = self.h_colors, self.h_rnds, self.h_image
+        return scene

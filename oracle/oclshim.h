@@ -7,7 +7,12 @@
 //
 // Canonical choices where OpenCL only bounds the result in ulps (stated):
 //   half_sqrt(x) = sqrtf(x) (correctly rounded)      normalize(v) = v / sqrtf(dot(v,v))
-//   dot(a,b) = (a.x*b.x + a.y*b.y) + a.z*b.z          pow/cos/sin  = glibc powf/cosf/sinf
+//   dot(a,b) = (a.x*b.x + a.y*b.y) + a.z*b.z
+//   pow/cos/sin = the CORRECTLY ROUNDED float result, obtained as (float)f((double)x) with glibc's
+//                 double-precision functions (< 1 ulp in double, so the narrowed value is the correctly
+//                 rounded float except for arguments within ~2^-29 relative of a rounding boundary).
+//                 This is the one choice every implementation can reproduce: the CUDA parity build
+//                 evaluates the same expression with CUDA's double functions.
 //   fmin/fmax = fminf/fmaxf (NaN → the other operand, as OpenCL specifies)
 // and the translation unit is compiled with -ffp-contract=off (no FMA).
 #ifndef ORACLE_OCLSHIM_H_
@@ -60,10 +65,10 @@ inline float half_sqrt(float x) { return sqrtf(x); }
 inline float fabs(float x) { return fabsf(x); }
 inline float fmin(float a, float b) { return fminf(a, b); }
 inline float fmax(float a, float b) { return fmaxf(a, b); }
-inline float pow(float a, float b) { return powf(a, b); }
-inline float pow(float a, int b) { return powf(a, (float)b); }
-inline float cos(float a) { return cosf(a); }
-inline float sin(float a) { return sinf(a); }
+inline float pow(float a, float b) { return (float)::pow((double)a, (double)b); }
+inline float pow(float a, int b) { return (float)::pow((double)a, (double)b); }
+inline float cos(float a) { return (float)::cos((double)a); }
+inline float sin(float a) { return (float)::sin((double)a); }
 inline float max(float a, float b) { return a < b ? b : a; }
 inline float3 max(float s, float3 v) { return float3_(max(s, v.x), max(s, v.y), max(s, v.z)); }
 inline float3 max(float3 v, float s) { return float3_(max(v.x, s), max(v.y, s), max(v.z, s)); }

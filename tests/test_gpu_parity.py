@@ -1,0 +1,161 @@
+"""GPU parity: the CUDA path, driven through the C-ABI exactly as the reference host drives OpenCL,
+against the reference's own prog.cl executed on the CPU (oracle/_ref/ref_cpu) on the same scene,
+camera and per-pixel seeds.
+
+Tolerances (written here):
+  * PARITY arithmetic: colors and RNG states are expected BIT-IDENTICAL to the oracle; the test
+    allows <= 1e-5 of the pixels to differ (double-function rounding boundary cases, see oclshim.h).
+  * FAST arithmetic (FMA, rsqrt, sincospi): >= 99.9 % of pixels within 1e-4 relative and image RMSE
+    <= 1 % of the mean radiance at fixed spp.
+"""
+import numpy as np
+import pytest
+
+from opencl_path_tracer_b200 import capi, host
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+W, H, SPP, DEPTH = 160, 120, 6, 4
+
+
+@pytest.fixture(scope="module")
+def cornell_ref():
+    if not util.have_ref_cpu():
+        pytest.skip("oracle/_ref/ref_cpu not built")
+    return util.run_ref_cpu(W, H, SPP, DEPTH, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3)
+
+
+def render(ptb, ref, accel, math, mode, spp=SPP):
+    surf = host.load_ptbd(ref["files"]["dump"])
+    ptb.set_accel(accel)
+    ptb.set_math(math)
+    s = host.scene_from_surface(surf, ptb)
+    if mode == "two_kernel":          # literal gen_ray + trace_ray launches per sample, unfused
+        ptb.set_fuse_gen(0)
+        for _ in range(spp):
+            s.render()
+    elif mode == "fused_launches":    # same calls, gen_ray folded into trace_ray
+        ptb.set_fuse_gen(1)
+        for _ in range(spp):
+            s.render()
+    else:                             # in-kernel sample loop
+        s.render_spp(spp)
+    ptb.finish()
+    ptb.set_fuse_gen(1)
+    return s.download_colors(), s.download_rnds()
+
+
+@pytest.mark.parametrize("accel", [capi.ACCEL_BRUTE, capi.ACCEL_REFBVH, capi.ACCEL_LBVH])
+@pytest.mark.parametrize("mode", ["two_kernel", "fused_launches", "render_spp"])
+def test_parity_math_is_bit_identical(ptb, cornell_ref, accel, mode):
+    colors, rnds = render(ptb, cornell_ref, accel, capi.MATH_PARITY, mode)
+    st = util.compare(colors, cornell_ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-5, st
+    assert (rnds == cornell_ref["rnds"]).mean() >= 1.0 - 1e-5
+
+
+@pytest.mark.parametrize("accel", [capi.ACCEL_BRUTE, capi.ACCEL_LBVH])
+def test_fast_math_within_tolerance(ptb, cornell_ref, accel):
+    colors, _ = render(ptb, cornell_ref, accel, capi.MATH_FAST, "render_spp")
+    st = util.compare(colors, cornell_ref["colors"])
+    assert st["frac_rel_le_1e-4"] >= 0.999, st
+    assert st["rmse_over_mean"] <= 0.01, st
+
+
+def test_depth1_preview_is_exact(ptb):
+    """iterations == 1: flat kd+emission preview (prog.cl:323-325) — a sharp test of ray generation + closest hit."""
+    if not util.have_ref_cpu():
+        pytest.skip("oracle/_ref/ref_cpu not built")
+    ref = util.run_ref_cpu(W, H, 2, 1, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3)
+    colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=2)
+    st = util.compare(colors, ref["colors"])
+    assert st["bit_equal_frac"] == 1.0, st
+    assert (rnds == ref["rnds"]).all()
+
+
+def test_work_counters_match_reference(ptb):
+    """rays / box tests / triangle tests of the REFBVH traversal equal the reference's own counts."""
+    if not util.have_ref_cpu():
+        pytest.skip("oracle/_ref/ref_cpu not built")
+    ref = util.run_ref_cpu(96, 64, 2, 4, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3, count=True)
+    surf = host.load_ptbd(ref["files"]["dump"])
+    ptb.set_accel(capi.ACCEL_REFBVH)
+    ptb.set_math(capi.MATH_PARITY)
+    ptb.set_count_work(1)
+    ptb.reset_counters()
+    s = host.scene_from_surface(surf, ptb)
+    s.render_spp(2)
+    c = ptb.counters()
+    ptb.set_count_work(0)
+    for k in ("rays", "box_tests", "tri_tests", "tri_stage1", "tri_stage2", "tri_stage3"):
+        assert c[k] == ref["info"][k], (k, c, ref["info"])
+
+
+# ---------------------------------------------------------------- every material type, many objects
+@pytest.fixture(scope="module")
+def mixed_ref(tmp_path_factory):
+    if not util.have_ref_cpu():
+        pytest.skip("oracle/_ref/ref_cpu not built")
+    from opencl_path_tracer_b200 import scenes
+    d = scenes.describe("small_mixed")
+    path = str(tmp_path_factory.mktemp("scenes") / "small_mixed.ptbs")
+    scenes.write_ptbs(d, path)
+    return util.run_ref_cpu(W, H, 8, 6, tribin=path, eye=d["eye"], fov=d["fov"])
+
+
+@pytest.mark.parametrize("accel", [capi.ACCEL_BRUTE, capi.ACCEL_REFBVH, capi.ACCEL_LBVH])
+def test_mixed_materials_parity(ptb, mixed_ref, accel):
+    """mirror (type 1), glass (type 2), glossy lobe (ks != 0) and emitter paths, depth 6, 770 triangles in 4 objects."""
+    colors, rnds = render(ptb, mixed_ref, accel, capi.MATH_PARITY, "render_spp", spp=8)
+    st = util.compare(colors, mixed_ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+    assert (rnds == mixed_ref["rnds"]).mean() >= 1.0 - 1e-4
+
+
+def test_mixed_materials_fast(ptb, mixed_ref):
+    colors, _ = render(ptb, mixed_ref, capi.ACCEL_LBVH, capi.MATH_FAST, "render_spp", spp=8)
+    st = util.compare(colors, mixed_ref["colors"])
+    assert st["frac_rel_le_1e-4"] >= 0.995, st          # glass/mirror chains amplify rounding: 99.5 % here
+    assert st["rmse_over_mean"] <= 0.05, st
+
+
+# ---------------------------------------------------------------- 100 k triangles: LBVH == reference trees == oracle
+@pytest.fixture(scope="module")
+def spheres_ref(tmp_path_factory):
+    if not util.have_ref_cpu():
+        pytest.skip("oracle/_ref/ref_cpu not built")
+    from opencl_path_tracer_b200 import scenes
+    d = scenes.describe("spheres100k")
+    path = str(tmp_path_factory.mktemp("scenes") / "spheres100k.ptbs")
+    scenes.write_ptbs(d, path)
+    return util.run_ref_cpu(192, 108, 4, 4, tribin=path, eye=d["eye"], fov=d["fov"])
+
+
+@pytest.mark.parametrize("accel", [capi.ACCEL_REFBVH, capi.ACCEL_LBVH])
+def test_spheres100k_parity(ptb, spheres_ref, accel):
+    colors, rnds = render(ptb, spheres_ref, accel, capi.MATH_PARITY, "render_spp", spp=4)
+    st = util.compare(colors, spheres_ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+    assert (rnds == spheres_ref["rnds"]).mean() >= 1.0 - 1e-4
+
+
+# ---------------------------------------------------------------- the reference's own host drives the CUDA library
+def test_reference_host_over_cuda_shim(tmp_path):
+    """oracle/_ref/ref_host_b200 = /root/reference/main.cpp compiled UNMODIFIED (but for the resolution constants)
+    behind shim/CL/cl.hpp, linked against libptb200.so: same Scene methods, same launches, CUDA underneath."""
+    import json, os, subprocess
+    exe = os.path.join(util.ROOT, "oracle", "_ref", "ref_host_b200")
+    if not (os.access(exe, os.X_OK) and util.have_ref_cpu()):
+        pytest.skip("oracle/_ref binaries not built")
+    ref = util.run_ref_cpu(128, 96, 5, 4, obj=util.CORNELL, want=("colors", "rnds"))
+    out = str(tmp_path / "cuda.bin")
+    r = subprocess.run([exe, "--w", "128", "--h", "96", "--spp", "5", "--iterations", "4", "--obj", util.CORNELL, "--pos", "555", "0", "0",
+                        "--math", "0", "--out", out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    info = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert info["backend"] == "cuda-sm100a" and info["error"] == ""
+    colors = np.fromfile(out, dtype=np.float32).reshape(96, 128, 4)
+    st = util.compare(colors, ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+    assert info["rays"] == ref["info"]["rays"]
