@@ -186,7 +186,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     ptb = capi.Ptb(local)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)      # a real (non-default) stream: the kernels and the timing events share it
+    torch.cuda.set_stream(stream)
     ptb.set_stream(stream.cuda_stream)
     ptb.set_math(capi.MATH_FAST if args.math == "fast" else capi.MATH_PARITY)
     ptb.set_accel({"auto": 0, "brute": 1, "refbvh": 2, "lbvh": 3}[args.accel])

@@ -108,13 +108,15 @@ __global__ void k_morton(const float4 *q0, const float4 *q1, const float4 *q2, i
     vals[i] = i;
 }
 
-__global__ void k_gather(const float4 *q0, const float4 *q1, const float4 *q2, const int *vals, int n,
-                         float4 *sq0, float4 *sq1, float4 *sq2, float4 *leaf_lo, float4 *leaf_hi) {
+__global__ void k_gather(const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
+                         const int *vals, int n, float4 *sq0, float4 *sq1, float4 *sq2, float4 *sf0, float4 *sf1, float4 *sf2,
+                         float4 *leaf_lo, float4 *leaf_hi) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int i = vals[pos];
     float4 a = q0[i], b = q1[i], c = q2[i];
     sq0[pos] = a; sq1[pos] = b; sq2[pos] = c;
+    sf0[pos] = f0[i]; sf1[pos] = f1[i]; sf2[pos] = f2[i];
     Box bx = tri_box(a, b, c);
     leaf_lo[pos] = make_float4(bx.lo[0], bx.lo[1], bx.lo[2], 0.0f);
     leaf_hi[pos] = make_float4(bx.hi[0], bx.hi[1], bx.hi[2], 0.0f);
@@ -239,7 +241,7 @@ template <typename T> cudaError_t dalloc(T **p, size_t count) { return cudaMallo
 
 void lbvh_free(Lbvh *b) {
     if (!b) return;
-    cudaFree(b->bvh); cudaFree(b->sq0); cudaFree(b->sq1); cudaFree(b->sq2); cudaFree(b->sorted_id);
+    cudaFree(b->bvh); cudaFree(b->sq0); cudaFree(b->sq1); cudaFree(b->sq2); cudaFree(b->sf0); cudaFree(b->sf1); cudaFree(b->sf2); cudaFree(b->sorted_id);
     cudaFree(b->range); cudaFree(b->child); cudaFree(b->leaf_lo); cudaFree(b->leaf_hi); cudaFree(b->node_lo); cudaFree(b->node_hi);
     memset(b, 0, sizeof(*b));
 }
@@ -261,7 +263,8 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
     return 0;
 }
 
-int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, int n, int leaf_size, cudaStream_t st, char *err, size_t errcap) {
+int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
+               int n, int leaf_size, cudaStream_t st, char *err, size_t errcap) {
     lbvh_free(b);
     b->n_tris = n;
     b->leaf_size = leaf_size < 1 ? 1 : (leaf_size > 8 ? 8 : leaf_size);
@@ -275,6 +278,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, in
     CK(dalloc(&bounds, 8)); CK(dalloc(&keys, n)); CK(dalloc(&keys2, n)); CK(dalloc(&vals, n)); CK(dalloc(&vals2, n));
     CK(dalloc(&pnode, n)); CK(dalloc(&pleaf, n)); CK(dalloc(&arrivals, n)); CK(dalloc(&stats, 4));
     CK(dalloc(&b->sq0, n)); CK(dalloc(&b->sq1, n)); CK(dalloc(&b->sq2, n)); CK(dalloc(&b->sorted_id, n));
+    CK(dalloc(&b->sf0, n)); CK(dalloc(&b->sf1, n)); CK(dalloc(&b->sf2, n));
     CK(dalloc(&b->leaf_lo, n)); CK(dalloc(&b->leaf_hi, n)); CK(dalloc(&b->node_lo, n)); CK(dalloc(&b->node_hi, n));
     CK(dalloc((int2 **)&b->range, n)); CK(dalloc((int2 **)&b->child, n)); CK(dalloc(&b->bvh, (size_t)4 * n));
 
@@ -289,7 +293,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, in
     void *tmp;
     CK(cudaMalloc(&tmp, tmp_bytes + 16));
     CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63, st));
-    k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, vals2, n, b->sq0, b->sq1, b->sq2, b->leaf_lo, b->leaf_hi);
+    k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, vals2, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi);
     CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
     b->launches += 1;
     CK(cudaMemsetAsync(stats, 0, 16, st));

@@ -8,7 +8,8 @@
 struct Lbvh {
     // traversal data
     float4 *bvh;                  // 4 float4 per node
-    float4 *sq0, *sq1, *sq2;      // triangles in Morton order
+    float4 *sq0, *sq1, *sq2;      // triangles in Morton order, parity layout (vertices + normal)
+    float4 *sf0, *sf1, *sf2;      // triangles in Morton order, fast layout (normal, anchor, barycentric gradients)
     int *sorted_id;               // Morton position → upload index
     int root;                     // root link
     // kept for re-emitting with a larger inflation (far-away camera)
@@ -19,7 +20,9 @@ struct Lbvh {
     unsigned long long launches;
 };
 
-int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, int n, int leaf_size, cudaStream_t st, char *err, size_t errcap);
+// q*: staged triangles in upload order (parity layout, holds the vertices); f*: the same triangles in the fast layout
+int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
+               int n, int leaf_size, cudaStream_t st, char *err, size_t errcap);
 // rewrite the traversal nodes with boxes inflated for ray origins up to `reach` from the coordinate origin
 int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap);
 void lbvh_free(Lbvh *b);

@@ -63,51 +63,74 @@ PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2,
 }
 
 // ---------------------------------------------------------------- ray–triangle (prog.cl:94-112)
-// Returns true and t when the reference's test accepts; the caller applies first_intersect's
-// "t > 0 and strictly closer" rule.  NaN t (dot(V,N)==0) falls through the comparisons like there.
+// BRANCH-FREE: every lane evaluates the whole test and the acceptance is a predicate, so a warp
+// that scans a triangle list stays converged (the early returns of the reference cost ~3x in
+// divergence: measured 11 of 32 lanes active, profiles/r01_*).  The predicate equals the
+// reference's nested ifs, NaNs included: accept <=> !(t<0) && e1>=0 && e2>=0 && e3>=0.
+//
+// The three float4 of a triangle mean different things in the two arithmetic flavours:
+//   parity: (r1,N.x) (r2,N.y) (r3,N.z)  — the uploaded record, evaluated with prog.cl's own expressions
+//   fast:   (N, r1.x) (r1.y, r1.z, mu.x, mu.y) (mu.z, mv)  — unit normal, anchor vertex and the two
+//           barycentric gradients mu = (e2 x N)/(N.(e1 x e2)), mv = (N x e1)/(N.(e1 x e2)) precomputed at
+//           upload (ptb_abi.cu): u = mu.w, v = mv.w with w = p - r1; inside <=> u>=0, v>=0, u+v<=1, the
+//           same three half-planes as the reference's edge tests (edge1 <=> v>=0, edge3 <=> u>=0, edge2 <=> u+v<=1)
+#if PT_PARITY
+PT_DEV V3 tri_normal(float4 a, float4 b, float4 c) { return v3(a.w, b.w, c.w); }
 template <bool COUNT>
-PT_DEV bool triangle_intersect(float4 q0, float4 q1, float4 q2, V3 P, V3 V, float &t_out, Work &wk) {
+PT_DEV bool tri_accept(float4 q0, float4 q1, float4 q2, V3 P, V3 V, float &t, Work &wk) {
     V3 r1 = v3(q0), r2 = v3(q1), r3 = v3(q2), N = v3(q0.w, q1.w, q2.w);
-    if (COUNT) wk.tri++;
-    float t = pt_div(dot(r1 - P, N), dot(V, N));
-    if (t < 0.0f) return false;
-    if (COUNT) wk.tri1++;
+    t = pt_div(dot(r1 - P, N), dot(V, N));
     V3 p = P + V * t;
-    if (dot(cross(r2 - r1, p - r1), N) >= 0.0f) {
-        if (COUNT) wk.tri2++;
-        if (dot(cross(r3 - r2, p - r2), N) >= 0.0f) {
-            if (COUNT) wk.tri3++;
-            if (dot(cross(r1 - r3, p - r3), N) >= 0.0f) {
-                t_out = t;
-                return true;
-            }
-        }
-    }
-    return false;
+    const bool s0 = !(t < 0.0f);
+    const bool s1 = dot(cross(r2 - r1, p - r1), N) >= 0.0f;
+    const bool s2 = dot(cross(r3 - r2, p - r2), N) >= 0.0f;
+    const bool s3 = dot(cross(r1 - r3, p - r3), N) >= 0.0f;
+    if (COUNT) { wk.tri++; wk.tri1 += s0; wk.tri2 += s0 & s1; wk.tri3 += s0 & s1 & s2; }
+    return s0 & s1 & s2 & s3;
 }
+#else
+PT_DEV V3 tri_normal(float4 a, float4, float4) { return v3(a.x, a.y, a.z); }
+template <bool COUNT>
+PT_DEV bool tri_accept(float4 A, float4 B, float4 C, V3 P, V3 V, float &t, Work &wk) {
+    const V3 N = v3(A.x, A.y, A.z);
+    const V3 w0 = v3(A.w - P.x, B.x - P.y, B.y - P.z);          // r1 - P
+    t = dot(w0, N) * pt_rcp_approx(dot(V, N));
+    const V3 w = V * t - w0;                                     // p - r1
+    const float u = dot(v3(B.z, B.w, C.x), w);
+    const float v = dot(v3(C.y, C.z, C.w), w);
+    const float k = fminf(fminf(u, v), 1.0f - (u + v));
+    if (COUNT) { wk.tri++; const bool s0 = !(t < 0.0f); wk.tri1 += s0; wk.tri2 += s0 & (v >= 0.0f); wk.tri3 += s0 & (v >= 0.0f) & (u + v <= 1.0f); }
+    return k >= 0.0f;                                            // t > 0 is applied by closest_update (t NaN fails it)
+}
+#endif
 
 struct Closest {
-    float t;     // -1: none (init_Hit, prog.cl:68-70)
+    float t;     // +inf: none yet (converted to the reference's -1 by the caller)
     int tri;     // index in upload order
 };
+#define PT_NO_HIT __int_as_float(0x7f800000)
 
-// first_intersect over a range held in shared memory (prog.cl:113-122): strict '<' keeps the lowest index on ties
+// first_intersect (prog.cl:113-122): accept t > 0 and strictly closer — the lowest index wins ties
+PT_DEV void closest_update(Closest &best, bool accept, float t, int i) {
+    const bool better = accept & (t > 0.0f) & (t < best.t);
+    best.t = better ? t : best.t;
+    best.tri = better ? i : best.tri;
+}
 template <bool COUNT>
 PT_DEV void brute_smem(const float4 *s_tris, int n, V3 P, V3 V, Closest &best, Work &wk) {
+#pragma unroll 4
     for (int i = 0; i < n; ++i) {
         float t;
-        if (triangle_intersect<COUNT>(s_tris[3 * i], s_tris[3 * i + 1], s_tris[3 * i + 2], P, V, t, wk)) {
-            if (t > 0.0f && (best.t < 0.0f || t < best.t)) { best.t = t; best.tri = i; }
-        }
+        const bool acc = tri_accept<COUNT>(s_tris[3 * i], s_tris[3 * i + 1], s_tris[3 * i + 2], P, V, t, wk);
+        closest_update(best, acc, t, i);
     }
 }
 template <bool COUNT>
 PT_DEV void brute_global(const SceneDev &sc, int from, int to, V3 P, V3 V, Closest &best, Work &wk) {
     for (int i = from; i < to; ++i) {
         float t;
-        if (triangle_intersect<COUNT>(ldg4(sc.q0 + i), ldg4(sc.q1 + i), ldg4(sc.q2 + i), P, V, t, wk)) {
-            if (t > 0.0f && (best.t < 0.0f || t < best.t)) { best.t = t; best.tri = i; }
-        }
+        const bool acc = tri_accept<COUNT>(ldg4(sc.q0 + i), ldg4(sc.q1 + i), ldg4(sc.q2 + i), P, V, t, wk);
+        closest_update(best, acc, t, i);
     }
 }
 
@@ -149,9 +172,11 @@ PT_DEV void refbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work
                     ptr = 2 * (ptr - shift) + shift;
                     descend = true;
                 } else {
-                    Closest leaf; leaf.t = -1.0f; leaf.tri = -1;
-                    brute_global<COUNT>(sc, trii.x, trii.y, P, D, leaf, wk);
-                    if (leaf.t > 0.0f && (best.t < 0.0f || leaf.t < best.t)) { tmin = leaf.t; best = leaf; }
+                    // first_intersect over the leaf, then "keep track of the best hit" with strict '<' (prog.cl:168-172):
+                    // one running best in visit order is the same thing; tmin follows only real improvements
+                    const float before = best.t;
+                    brute_global<COUNT>(sc, trii.x, trii.y, P, D, best, wk);
+                    if (best.t < before) tmin = best.t;
                 }
             }
             if (!descend) {
@@ -179,7 +204,6 @@ PT_DEV void lbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &
     int stack[PT_LBVH_STACK];
     int sp = 0;
     int link = sc.bvh_root;
-    float tbest = 3.0e38f;
     for (;;) {
         while (link >= 0) {
             const float4 *nd = sc.bvh + 4 * (size_t)link;
@@ -195,8 +219,8 @@ PT_DEV void lbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &
             // widen both ends by 8 ulp (each product above carries <= 1.5 ulp)
             l0 -= fabsf(l0) * 1.0e-6f; l1 += fabsf(l1) * 1.0e-6f;
             r0 -= fabsf(r0) * 1.0e-6f; r1 += fabsf(r1) * 1.0e-6f;
-            const bool hl = l0 <= l1 && l1 >= 0.0f && l0 <= tbest;
-            const bool hr = r0 <= r1 && r1 >= 0.0f && r0 <= tbest;
+            const bool hl = l0 <= l1 && l1 >= 0.0f && l0 <= best.t;
+            const bool hr = r0 <= r1 && r1 >= 0.0f && r0 <= best.t;
             const int ll = __float_as_int(n3.x), lr = __float_as_int(n3.y);
             if (hl && hr) {
                 const bool left_first = l0 <= r0;
@@ -217,13 +241,10 @@ PT_DEV void lbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &
             for (int k = 0; k < count; ++k) {
                 const int pos = first + k;
                 float t;
-                if (triangle_intersect<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk)) {
-                    if (t > 0.0f) {
-                        const int id = __ldg(sc.sorted_id + pos);
-                        if (best.t < 0.0f || t < best.t || (t == best.t && id < best.tri)) {
-                            best.t = t; best.tri = id; tbest = t;
-                        }
-                    }
+                const bool acc = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
+                if (acc & (t > 0.0f) & (t <= best.t)) {
+                    const int id = __ldg(sc.sorted_id + pos);
+                    if (t < best.t || id < best.tri) { best.t = t; best.tri = id; }
                 }
             }
         }
@@ -281,19 +302,26 @@ PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32
     if (iterations == 1) ps.color = m.kd + m.emission;                       // flat preview, prog.cl:323-325
     V3 N = hitN;
     if (dot(rayD, N) > 0.0f) N = -N;                                        // prog.cl:326-328
-    if (m.type == 0) {                                                      // diffuse + Phong lobe, prog.cl:329-340
+    if (m.type == 0 || m.type == 3) {
+        // diffuse + Phong lobe (prog.cl:329-340) and emitter (prog.cl:358-366) share the cosine-weighted
+        // bounce, so the warp stays converged through the sampling code
+        const float intensity = pt_fmax(0.0f, dot(-rayD, N));               // emitter only: uses the OLD ray
         float r1 = pt_rand(rng), r2 = pt_rand(rng);
         V3 nP, nD;
         new_ray_diffuse(hitP, N, r1, r2, nP, nD);
-        float cos_theta = dot(nD, N);
-        ps.fL = ps.fL * (m.kd * pt_fmax(0.0f, cos_theta));
-        if (m.ks.x == 0.0f && m.ks.y == 0.0f && m.ks.z == 0.0f && m.shininess >= 0.0f) {
-            // ks == 0: ks*pow(..) is exactly +0 for any finite pow (its base is in [0,1]), skip the pow
-            ps.fB = ps.fB * v3(0.0f, 0.0f, 0.0f);
+        if (m.type == 0) {
+            float cos_theta = dot(nD, N);
+            ps.fL = ps.fL * (m.kd * pt_fmax(0.0f, cos_theta));
+            if (m.ks.x == 0.0f && m.ks.y == 0.0f && m.ks.z == 0.0f && m.shininess >= 0.0f) {
+                // ks == 0: ks*pow(..) is exactly +0 for any finite pow (its base is in [0,1]), skip the pow
+                ps.fB = ps.fB * v3(0.0f, 0.0f, 0.0f);
+            } else {
+                V3 halfway = normalize(normalize(eye - hitP) + nD);
+                float cos_delta = dot(N, halfway);
+                ps.fB = ps.fB * (m.ks * pt_pow(pt_fmax(0.0f, cos_delta), m.shininess));
+            }
         } else {
-            V3 halfway = normalize(normalize(eye - hitP) + nD);
-            float cos_delta = dot(N, halfway);
-            ps.fB = ps.fB * (m.ks * pt_pow(pt_fmax(0.0f, cos_delta), m.shininess));
+            ps.color = ps.color + (((m.emission * (ps.fL + ps.fB)) * ps.fS) * ps.fR) * intensity;
         }
         rayP = nP; rayD = nD;
     } else if (m.type == 1) {                                               // mirror, prog.cl:341-345
@@ -318,11 +346,6 @@ PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32
         }
         if (before != ps.in) ps.fR = (ps.fR * (1.0f - F)) * (1.0f / (1.0f - prob));
         else ps.fR = (ps.fR * F) * (1.0f / prob);
-    } else if (m.type == 3) {                                               // emitter, prog.cl:358-366
-        float intensity = pt_fmax(0.0f, dot(-rayD, N));
-        float r1 = pt_rand(rng), r2 = pt_rand(rng);
-        new_ray_diffuse(hitP, N, r1, r2, rayP, rayD);
-        ps.color = ps.color + (((m.emission * (ps.fL + ps.fB)) * ps.fS) * ps.fR) * intensity;
     }
     // any other type: ray unchanged, nothing added
 }
@@ -388,7 +411,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
             }
             if (alive) {
                 wk.rays++;
-                Closest best; best.t = -1.0f; best.tri = -1;
+                Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
                 if (ACCEL == PT_ACCEL_BRUTE) {
                     if (SMEM) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
                     else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
@@ -397,10 +420,10 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
                 } else {
                     lbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
                 }
-                if (best.t > 0.0f) {
+                if (best.t < PT_NO_HIT) {
                     // Hit record of triangle_intersect (prog.cl:107): p = P + V*t, N = tri->N, mati
                     V3 hitP = rayP + rayD * best.t;
-                    V3 hitN = v3(ldg4(sc.q0 + best.tri).w, ldg4(sc.q1 + best.tri).w, ldg4(sc.q2 + best.tri).w);
+                    V3 hitN = tri_normal(ldg4(sc.q0 + best.tri), ldg4(sc.q1 + best.tri), ldg4(sc.q2 + best.tri));
                     Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
                     shade_hit(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
                     if (++depth == p.iterations) alive = false;

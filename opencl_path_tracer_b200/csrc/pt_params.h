@@ -18,7 +18,8 @@ enum {
 
 // Everything a path kernel reads about the scene.  Passed by value (lives in the constant bank).
 struct SceneDev {
-    // staged triangles in upload order (prog.cl:18-21 → 3 float4 planes, see ptb_types.h)
+    // staged triangles in upload order, 3 float4 planes in the layout of the arithmetic flavour that
+    // reads them (parity: vertices + normal; fast: normal, anchor, barycentric gradients — pt_kernels.cuh)
     const float4 *q0, *q1, *q2;
     const uint16_t *mati;
     int n_tris;
@@ -29,7 +30,7 @@ struct SceneDev {
     const int *kd_shift;
     int n_obj;
     // GPU-built LBVH (lbvh.cu)
-    const float4 *bvh;            // 2 float4 per node, LbvhNode
+    const float4 *bvh;            // 4 float4 per node: both children's boxes + links (lbvh.cu)
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)

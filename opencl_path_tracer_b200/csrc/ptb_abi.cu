@@ -43,7 +43,8 @@ struct Staged {                        // device-internal copy of the scene, val
     ptb_mem tris_handle = 0;
     unsigned long long tris_version = ~0ull;
     int n_tris = -1;
-    float4 *q0 = nullptr, *q1 = nullptr, *q2 = nullptr;
+    float4 *q0 = nullptr, *q1 = nullptr, *q2 = nullptr;   // parity layout: (r1,N.x) (r2,N.y) (r3,N.z)
+    float4 *f0 = nullptr, *f1 = nullptr, *f2 = nullptr;   // fast layout: (N,r1.x) (r1.yz,mu.xy) (mu.z,mv)
     uint16_t *mati = nullptr;
     int capacity = 0;
     Lbvh lbvh;
@@ -121,7 +122,8 @@ template <typename T> T arg_val(int k, int i, bool *ok) {
 MemObj *arg_mem(int k, int i) { return G.args[k][i].set ? find(G.args[k][i].mem) : nullptr; }
 
 // ---------------------------------------------------------------- staging (AoS upload → SoA planes)
-__global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 *q1, float4 *q2, uint16_t *mati) {
+__global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 *q1, float4 *q2,
+                             float4 *f0, float4 *f1, float4 *f2, uint16_t *mati) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 *t = reinterpret_cast<const float4 *>(tris + i);   // 5 x 16 B per record
@@ -130,6 +132,17 @@ __global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 
     q1[i] = make_float4(r2.x, r2.y, r2.z, N.y);
     q2[i] = make_float4(r3.x, r3.y, r3.z, N.z);
     mati[i] = tris[i].mati;
+    // fast layout: barycentric gradients mu = (e2 x N)/d, mv = (N x e1)/d with d = N.(e1 x e2), in double
+    double e1[3] = {(double)r2.x - r1.x, (double)r2.y - r1.y, (double)r2.z - r1.z};
+    double e2[3] = {(double)r3.x - r1.x, (double)r3.y - r1.y, (double)r3.z - r1.z};
+    double nn[3] = {N.x, N.y, N.z};
+    double cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+    double inv = 1.0 / (nn[0] * cx + nn[1] * cy + nn[2] * cz);
+    double mu[3] = {(e2[1] * nn[2] - e2[2] * nn[1]) * inv, (e2[2] * nn[0] - e2[0] * nn[2]) * inv, (e2[0] * nn[1] - e2[1] * nn[0]) * inv};
+    double mv[3] = {(nn[1] * e1[2] - nn[2] * e1[1]) * inv, (nn[2] * e1[0] - nn[0] * e1[2]) * inv, (nn[0] * e1[1] - nn[1] * e1[0]) * inv};
+    f0[i] = make_float4(N.x, N.y, N.z, r1.x);
+    f1[i] = make_float4(r1.y, r1.z, (float)mu[0], (float)mu[1]);
+    f2[i] = make_float4((float)mu[2], (float)mv[0], (float)mv[1], (float)mv[2]);
 }
 
 int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
@@ -138,17 +151,20 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
     if ((size_t)n_tris * sizeof(RefTriangle) > tris->bytes)
         return fail(PTB_ERR_INVALID_ARGS, "trace_ray: tris_size %d exceeds the triangle buffer (%zu bytes)", n_tris, tris->bytes);
     if (n_tris > s.capacity) {
-        cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.mati);
+        cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
         s.capacity = 0;
         size_t cap = (size_t)n_tris + 16;
         CUDA_OK(cudaMalloc((void **)&s.q0, cap * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.q1, cap * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.q2, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.f0, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.f1, cap * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.f2, cap * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.mati, cap * sizeof(uint16_t)));
         s.capacity = n_tris;
     }
     if (n_tris > 0) {
-        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.mati);
+        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.mati);
         CUDA_OK(cudaGetLastError());
         G.launches++;
     }
@@ -172,7 +188,7 @@ int ensure_lbvh(float reach) {
     err[0] = 0;
     if (!s.lbvh_valid || s.lbvh_leaf != G.lbvh_leaf) {
         unsigned long long before = s.lbvh.launches;
-        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.n_tris, G.lbvh_leaf, G.stream, err, sizeof err))
+        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.n_tris, G.lbvh_leaf, G.stream, err, sizeof err))
             return fail(PTB_ERR_DEVICE, "%s", err);
         G.launches += s.lbvh.launches - before + 4;   // + the radix-sort passes
         s.lbvh_valid = true;
@@ -213,7 +229,8 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     Staged &s = G.staged;
     bool have_tree = tree && shift && shift_size > 0 && shift->bytes >= (size_t)shift_size * 4;
     p.accel = resolve_accel(tris_size, have_tree);
-    p.sc.q0 = s.q0; p.sc.q1 = s.q1; p.sc.q2 = s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
+    const bool fastm = G.math == PTB_MATH_FAST;   // each arithmetic flavour reads its own triangle layout
+    p.sc.q0 = fastm ? s.f0 : s.q0; p.sc.q1 = fastm ? s.f1 : s.q1; p.sc.q2 = fastm ? s.f2 : s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
     p.sc.mats = (const RefMaterial *)mats->dptr;
     p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
     if (have_tree) {
@@ -225,7 +242,8 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         float reach = fmaxf(fabsf(p.cam.eye.x), fmaxf(fabsf(p.cam.eye.y), fabsf(p.cam.eye.z)));
         rc = ensure_lbvh(reach);
         if (rc) return rc;
-        p.sc.bvh = s.lbvh.bvh; p.sc.sq0 = s.lbvh.sq0; p.sc.sq1 = s.lbvh.sq1; p.sc.sq2 = s.lbvh.sq2;
+        p.sc.bvh = s.lbvh.bvh;
+        p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
     }
     p.rnds = (int *)rnds->dptr;
@@ -314,7 +332,7 @@ int ptb_shutdown(void) {
         if (kv.second.owned) cudaFree(kv.second.dptr);
     G.mems.clear();
     Staged &s = G.staged;
-    cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.mati);
+    cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
     lbvh_free(&s.lbvh);
     s = Staged();
     cudaFree(G.counters);
