@@ -383,64 +383,69 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
     const int id = y * p.W + x;
     bool mine = x < p.W && y < p.H;
     if (mine && p.shard_n > 1) mine = ((id / p.shard_group) % p.shard_n) == p.shard_rank;
-    if (mine) {
-        uint32_t rng = (uint32_t)p.rnds[id];
-        V3 acc = v3(0.0f, 0.0f, 0.0f);
-        if (p.sample0 != 0 || p.sum_mode) acc = v3(p.colors[id]);
-        const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
-        const int s_end = p.sample0 + p.spp;
-        int s = p.sample0;
-        int depth = 0;
-        bool alive = false;
-        V3 rayP = eye, rayD = v3(0.0f, 0.0f, 1.0f);
-        Path ps;
-        path_reset(ps);
-        for (;;) {
-            if (!alive) {
-                if (s == s_end) break;
-                if (p.from_rays) {                                   // drop-in trace_ray: gen_ray already ran
-                    const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
-                    rayP = v3(r[0]); rayD = v3(r[1]);
-                } else {                                             // gen_ray fused, prog.cl:384-389
-                    float r1 = pt_rand(rng), r2 = pt_rand(rng);
-                    camera_get_ray(id, p.cam, r1, r2, rayP, rayD);
-                }
-                path_reset(ps);
-                depth = 0;
-                alive = p.iterations > 0;
+    // No lane leaves before the loop ends: the loop is WARP-CONVERGED.  Every iteration starts with a
+    // warp vote, so all 32 lanes walk the intersection code together; a lane without work (pixel outside
+    // the image/shard, or all its samples done) rides along predicated off.  (Without the vote the
+    // compiler threads the miss -> regenerate path around the loop head and the warp splits for good:
+    // measured 13.7 of 32 lanes active, profiles/r01_render_v2.txt.)
+    uint32_t rng = mine ? (uint32_t)p.rnds[id] : 1u;
+    V3 acc = v3(0.0f, 0.0f, 0.0f);
+    if (mine && (p.sample0 != 0 || p.sum_mode)) acc = v3(p.colors[id]);
+    const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
+    const int s_end = p.sample0 + p.spp;
+    int s = mine ? p.sample0 : s_end;
+    int depth = 0;
+    bool alive = false;
+    V3 rayP = eye, rayD = v3(0.0f, 0.0f, 1.0f);
+    Path ps;
+    path_reset(ps);
+    for (;;) {
+        if (!alive && s < s_end) {                               // path regeneration: next sample of this pixel
+            if (p.from_rays) {                                   // drop-in trace_ray: gen_ray already ran
+                const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
+                rayP = v3(r[0]); rayD = v3(r[1]);
+            } else {                                             // gen_ray fused, prog.cl:384-389
+                float r1 = pt_rand(rng), r2 = pt_rand(rng);
+                camera_get_ray(id, p.cam, r1, r2, rayP, rayD);
             }
-            if (alive) {
-                wk.rays++;
-                Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
-                if (ACCEL == PT_ACCEL_BRUTE) {
-                    if (SMEM) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
-                    else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
-                } else if (ACCEL == PT_ACCEL_REFBVH) {
-                    refbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
-                } else {
-                    lbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
-                }
-                if (best.t < PT_NO_HIT) {
-                    // Hit record of triangle_intersect (prog.cl:107): p = P + V*t, N = tri->N, mati
-                    V3 hitP = rayP + rayD * best.t;
-                    V3 hitN = tri_normal(ldg4(sc.q0 + best.tri), ldg4(sc.q1 + best.tri), ldg4(sc.q2 + best.tri));
-                    Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
-                    shade_hit(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
-                    if (++depth == p.iterations) alive = false;
-                } else {
-                    alive = false;                                   // miss: break, prog.cl:367-376
-                }
+            path_reset(ps);
+            depth = 0;
+            alive = true;
+        }
+        if (!__any_sync(0xffffffffu, alive)) break;
+        const bool trace = alive && depth < p.iterations;        // iterations <= 0: the bounce loop body never runs
+        Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+        if (ACCEL == PT_ACCEL_BRUTE) {                           // converged scan: idle lanes scan too (free)
+            if (SMEM) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
+            else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
+        } else if (trace) {
+            if (ACCEL == PT_ACCEL_REFBVH) refbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
+            else lbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
+        }
+        if (alive) {
+            if (trace) wk.rays++;
+            if (trace && best.t < PT_NO_HIT) {
+                // Hit record of triangle_intersect (prog.cl:107): p = P + V*t, N = tri->N, mati
+                V3 hitP = rayP + rayD * best.t;
+                V3 hitN = tri_normal(ldg4(sc.q0 + best.tri), ldg4(sc.q1 + best.tri), ldg4(sc.q2 + best.tri));
+                Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
+                shade_hit(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
+                if (++depth >= p.iterations) alive = false;
+            } else {
+                alive = false;                                   // miss: break, prog.cl:367-376
             }
-            if (!alive) {                                            // sample finished, prog.cl:379
+            if (!alive) {                                        // sample finished, prog.cl:379
                 if (p.sum_mode) acc = acc + ps.color;
                 else acc = (acc * (float)s + ps.color) / (float)(s + 1);
                 ++s;
                 wk.samples++;
             }
         }
+    }
+    if (mine) {
         p.rnds[id] = (int)rng;
         p.colors[id] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-        if (p.tex) p.tex[id] = reinhard_tone_map(acc);               // prog.cl:380
+        if (p.tex) p.tex[id] = reinhard_tone_map(acc);           // prog.cl:380
     }
     // work counters: one atomic per warp and counter
     if (p.counters) {
