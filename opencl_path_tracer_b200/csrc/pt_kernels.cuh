@@ -20,6 +20,7 @@
 #error "define PT_NS"
 #endif
 
+#include <stdlib.h>
 #include "pt_math.cuh"
 #include "pt_params.h"
 
@@ -47,11 +48,13 @@ PT_DEV Mat load_material(const RefMaterial *mats, int i) {
 }
 
 // ---------------------------------------------------------------- camera (prog.cl:82-92)
-PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2, V3 &P, V3 &D) {
+// px, py: id % X and id / X — the fused kernel knows them from its thread coordinates when the launch
+// width equals the camera's XM (always, for the reference host), and skips the integer division
+PT_DEV void camera_get_ray_xy(int px, int py, const RefCamera &cam, float rnd1, float rnd2, V3 &P, V3 &D) {
     int X = (int)cam.XM;
     int Y = (int)cam.YM;
-    float x = (float)(id % X) + rnd1;
-    float y = (float)(id / X) + rnd2;
+    float x = (float)px + rnd1;
+    float y = (float)py + rnd2;
     float sx = pt_div(2.0f * x, (float)X) - 1.0f;
     float sy = pt_div(2.0f * y, (float)Y) - 1.0f;
     V3 right = v3(cam.right.x, cam.right.y, cam.right.z) * sx;
@@ -60,6 +63,10 @@ PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2,
     V3 p = (v3(cam.lookat.x, cam.lookat.y, cam.lookat.z) + right) + up;
     P = eye;
     D = normalize(p - eye);
+}
+PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2, V3 &P, V3 &D) {
+    int X = (int)cam.XM;
+    camera_get_ray_xy(id % X, id / X, cam, rnd1, rnd2, P, D);
 }
 
 // ---------------------------------------------------------------- ray–triangle (prog.cl:94-112)
@@ -133,6 +140,52 @@ PT_DEV void brute_global(const SceneDev &sc, int from, int to, V3 P, V3 V, Close
         closest_update(best, acc, t, i);
     }
 }
+
+#if !PT_PARITY
+// ---- Blackwell packed-FP32 scan: two triangles per step with FFMA2 / FADD2 / FMUL2 (sm_100 f32x2)
+// The brute-force scan is issue-bound (86 % issue-slot utilisation, profiles/r01_render_v3.txt), so
+// the fix is fewer instructions: lane .x of every float2 carries triangle 2j, lane .y triangle 2j+1,
+// and the 21 FP32 operations of the test issue once for both.  Shared-memory layout per pair,
+// 6 float4 (built by the block at kernel start from the fast per-triangle layout):
+//   (N.x N.y) (N.z -r1.x) (-r1.y -r1.z) (mu.x mu.y) (mu.z mv.x) (mv.y mv.z), each component as an (A,B) pair
+// With w0 = P - r1:  t = (N.w0) / (N.(-V)),  w = p - r1 = w0 + V t,  u = mu.w, v = mv.w, k = min(u, v, 1-u-v).
+struct RayPair {                 // the ray broadcast into both lanes
+    float2 Px, Py, Pz, Vx, Vy, Vz, nVx, nVy, nVz;
+};
+PT_DEV RayPair ray_pair(V3 P, V3 V) {
+    RayPair r;
+    r.Px = make_float2(P.x, P.x); r.Py = make_float2(P.y, P.y); r.Pz = make_float2(P.z, P.z);
+    r.Vx = make_float2(V.x, V.x); r.Vy = make_float2(V.y, V.y); r.Vz = make_float2(V.z, V.z);
+    r.nVx = make_float2(-V.x, -V.x); r.nVy = make_float2(-V.y, -V.y); r.nVz = make_float2(-V.z, -V.z);
+    return r;
+}
+PT_DEV float2 dot2(float2 ax, float2 ay, float2 az, float2 bx, float2 by, float2 bz) {
+    return __ffma2_rn(az, bz, __ffma2_rn(ay, by, __fmul2_rn(ax, bx)));
+}
+template <int U>
+PT_DEV void brute_smem_pairs(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Closest &best) {
+    const RayPair r = ray_pair(P, V);
+    const float2 one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
+#pragma unroll U
+    for (int j = 0; j < n_pairs; ++j) {
+        const float4 L0 = s_pairs[6 * j], L1 = s_pairs[6 * j + 1], L2 = s_pairs[6 * j + 2];
+        const float4 L3 = s_pairs[6 * j + 3], L4 = s_pairs[6 * j + 4], L5 = s_pairs[6 * j + 5];
+        const float2 Nx = make_float2(L0.x, L0.y), Ny = make_float2(L0.z, L0.w), Nz = make_float2(L1.x, L1.y);
+        const float2 wx = __fadd2_rn(make_float2(L1.z, L1.w), r.Px);          // w0 = P - r1
+        const float2 wy = __fadd2_rn(make_float2(L2.x, L2.y), r.Py);
+        const float2 wz = __fadd2_rn(make_float2(L2.z, L2.w), r.Pz);
+        const float2 a = dot2(Nx, Ny, Nz, wx, wy, wz);                         // N.(P - r1)
+        const float2 b = dot2(Nx, Ny, Nz, r.nVx, r.nVy, r.nVz);                // N.(-V)
+        const float2 t = __fmul2_rn(a, make_float2(pt_rcp_approx(b.x), pt_rcp_approx(b.y)));
+        const float2 px = __ffma2_rn(r.Vx, t, wx), py = __ffma2_rn(r.Vy, t, wy), pz = __ffma2_rn(r.Vz, t, wz);   // p - r1
+        const float2 u = dot2(make_float2(L3.x, L3.y), make_float2(L3.z, L3.w), make_float2(L4.x, L4.y), px, py, pz);
+        const float2 v = dot2(make_float2(L4.z, L4.w), make_float2(L5.x, L5.y), make_float2(L5.z, L5.w), px, py, pz);
+        const float2 q = __ffma2_rn(__fadd2_rn(u, v), neg1, one);              // 1 - (u + v)
+        closest_update(best, fminf(fminf(u.x, v.x), q.x) >= 0.0f, t.x, 2 * j);
+        closest_update(best, fminf(fminf(u.y, v.y), q.y) >= 0.0f, t.y, 2 * j + 1);
+    }
+}
+#endif
 
 // ---------------------------------------------------------------- reference trees (prog.cl:123-184)
 // BBox_intersection with true divisions and OpenCL fmin/fmax NaN rules; kd_intersect's control flow:
@@ -285,6 +338,15 @@ PT_DEV void new_ray_specular(V3 hitP, V3 N, V3 oldD, V3 &P, V3 &D) {
     P = hitP + N * 0.001f;
 }
 
+// colors = (colors*s + color)/(s+1), prog.cl:379 — the parity flavour divides, the fast one multiplies by 1/(s+1)
+PT_DEV V3 pt_mean_step(V3 acc, V3 color, int s) {
+#if PT_PARITY
+    return (acc * (float)s + color) / (float)(s + 1);
+#else
+    return (acc * (float)s + color) * pt_rcp_approx((float)(s + 1));
+#endif
+}
+
 // per-path throughput state of trace_ray (prog.cl:307-316)
 struct Path {
     V3 fL, fB, fS, fR, color;
@@ -363,11 +425,11 @@ PT_DEV float4 reinhard_tone_map(V3 c) {
 #define PT_BLOCK 128
 #define PT_SMEM_MAX_TRIS 4096   // 192 KB of triangles at most in shared memory
 
-template <int ACCEL, bool COUNT, bool SMEM>
-__global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
+template <int ACCEL, bool COUNT, int SMEM, int MINB, int U>
+__global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p) {
     extern __shared__ float4 s_tris[];
     const SceneDev &sc = p.sc;
-    if (ACCEL == PT_ACCEL_BRUTE && SMEM) {
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 1) {
         for (int i = threadIdx.x; i < sc.n_tris; i += PT_BLOCK) {
             s_tris[3 * i] = ldg4(sc.q0 + i);
             s_tris[3 * i + 1] = ldg4(sc.q1 + i);
@@ -375,6 +437,24 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
         }
         __syncthreads();
     }
+#if !PT_PARITY
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) {      // pair layout for the packed-FP32 scan
+        const int n_pairs = (sc.n_tris + 1) >> 1;
+        for (int j = threadIdx.x; j < n_pairs; j += PT_BLOCK) {
+            const int ia = 2 * j, ib = 2 * j + 1;
+            const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);     // padding triangle: N = 0 -> t = NaN -> never accepted
+            const float4 A0 = ldg4(sc.q0 + ia), A1 = ldg4(sc.q1 + ia), A2 = ldg4(sc.q2 + ia);
+            const float4 B0 = ib < sc.n_tris ? ldg4(sc.q0 + ib) : z, B1 = ib < sc.n_tris ? ldg4(sc.q1 + ib) : z, B2 = ib < sc.n_tris ? ldg4(sc.q2 + ib) : z;
+            s_tris[6 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);          // N.x N.y
+            s_tris[6 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);        // N.z -r1.x
+            s_tris[6 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);      // -r1.y -r1.z
+            s_tris[6 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);          // mu.x mu.y
+            s_tris[6 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);          // mu.z mv.x
+            s_tris[6 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);          // mv.y mv.z
+        }
+        __syncthreads();
+    }
+#endif
     // warp → 8x4 pixel tile, block → 16x8
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
@@ -394,6 +474,8 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
     const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
     const int s_end = p.sample0 + p.spp;
     int s = mine ? p.sample0 : s_end;
+    const int camX = (int)p.cam.XM;
+    const int cam_x = camX == p.W ? x : id % max(camX, 1), cam_y = camX == p.W ? y : id / max(camX, 1);
     int depth = 0;
     bool alive = false;
     V3 rayP = eye, rayD = v3(0.0f, 0.0f, 1.0f);
@@ -406,7 +488,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
                 rayP = v3(r[0]); rayD = v3(r[1]);
             } else {                                             // gen_ray fused, prog.cl:384-389
                 float r1 = pt_rand(rng), r2 = pt_rand(rng);
-                camera_get_ray(id, p.cam, r1, r2, rayP, rayD);
+                camera_get_ray_xy(cam_x, cam_y, p.cam, r1, r2, rayP, rayD);
             }
             path_reset(ps);
             depth = 0;
@@ -416,7 +498,10 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
         const bool trace = alive && depth < p.iterations;        // iterations <= 0: the bounce loop body never runs
         Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
         if (ACCEL == PT_ACCEL_BRUTE) {                           // converged scan: idle lanes scan too (free)
-            if (SMEM) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
+#if !PT_PARITY
+            if (SMEM == 2) brute_smem_pairs<U>(s_tris, (sc.n_tris + 1) >> 1, rayP, rayD, best); else
+#endif
+            if (SMEM == 1) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
             else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
         } else if (trace) {
             if (ACCEL == PT_ACCEL_REFBVH) refbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
@@ -436,7 +521,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_render(const RenderParams p) {
             }
             if (!alive) {                                        // sample finished, prog.cl:379
                 if (p.sum_mode) acc = acc + ps.color;
-                else acc = (acc * (float)s + ps.color) / (float)(s + 1);
+                else acc = pt_mean_step(acc, ps.color, s);
                 ++s;
                 wk.samples++;
             }
@@ -477,25 +562,36 @@ __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n)
 }
 
 // ---------------------------------------------------------------- host-side dispatch
-template <int ACCEL, bool COUNT, bool SMEM>
+template <int ACCEL, bool COUNT, int SMEM, int MINB = 1, int U = 2>
 static void launch_one(const RenderParams &p, cudaStream_t st) {
     dim3 grid((p.W + 15) / 16, (p.H + 7) / 8);
-    size_t smem = (ACCEL == PT_ACCEL_BRUTE && SMEM) ? (size_t)p.sc.n_tris * 3 * sizeof(float4) : 0;
+    size_t smem = 0;
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 1) smem = (size_t)p.sc.n_tris * 3 * sizeof(float4);
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) smem = (size_t)((p.sc.n_tris + 1) / 2) * 6 * sizeof(float4);
     if (smem > 48 * 1024)
-        cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_render<ACCEL, COUNT, SMEM><<<grid, PT_BLOCK, smem, st>>>(p);
+        cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM, MINB, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_render<ACCEL, COUNT, SMEM, MINB, U><<<grid, PT_BLOCK, smem, st>>>(p);
 }
 
 void launch_render(const RenderParams &p, cudaStream_t st) {
     const bool c = p.count_work != 0;
     if (p.accel == PT_ACCEL_BRUTE) {
         const bool smem = p.sc.n_tris <= PT_SMEM_MAX_TRIS;
-        if (smem) { if (c) launch_one<PT_ACCEL_BRUTE, true, true>(p, st); else launch_one<PT_ACCEL_BRUTE, false, true>(p, st); }
-        else      { if (c) launch_one<PT_ACCEL_BRUTE, true, false>(p, st); else launch_one<PT_ACCEL_BRUTE, false, false>(p, st); }
+        if (smem) {
+            if (c) launch_one<PT_ACCEL_BRUTE, true, 1>(p, st);
+#if !PT_PARITY
+            else launch_one<PT_ACCEL_BRUTE, false, 2, 8, 4>(p, st);   // packed-FP32 pair scan; 64 registers -> 8 blocks/SM, 4 pairs in flight
+                                                                      // (measured best of 8 (occupancy, unroll) variants: 23.0 vs 20.7 Grays/s)
+#else
+            else launch_one<PT_ACCEL_BRUTE, false, 1>(p, st);
+#endif
+        } else {
+            if (c) launch_one<PT_ACCEL_BRUTE, true, 0>(p, st); else launch_one<PT_ACCEL_BRUTE, false, 0>(p, st);
+        }
     } else if (p.accel == PT_ACCEL_REFBVH) {
-        if (c) launch_one<PT_ACCEL_REFBVH, true, false>(p, st); else launch_one<PT_ACCEL_REFBVH, false, false>(p, st);
+        if (c) launch_one<PT_ACCEL_REFBVH, true, 0>(p, st); else launch_one<PT_ACCEL_REFBVH, false, 0>(p, st);
     } else {
-        if (c) launch_one<PT_ACCEL_LBVH, true, false>(p, st); else launch_one<PT_ACCEL_LBVH, false, false>(p, st);
+        if (c) launch_one<PT_ACCEL_LBVH, true, 0>(p, st); else launch_one<PT_ACCEL_LBVH, false, 0>(p, st);
     }
 }
 
