@@ -1,0 +1,87 @@
+"""Host-side mirror of the reference's Scene interface (opencl_path_tracer_b200/host.py) against dumps of the
+kernel-argument surface written by the reference's own host code (main.cpp compiled unmodified)."""
+import os
+
+import numpy as np
+import pytest
+
+from opencl_path_tracer_b200 import host, scenes
+from tests import util
+
+
+class _NoDevice:
+    """host.Scene's record building needs no device."""
+
+
+def fields_equal(a, b, fields):
+    for f in fields:
+        x, y = a[f], b[f]
+        if x.ndim >= 1 and x.shape[-1] == 4:      # float3: lane 3 is padding (uninitialised in the reference)
+            x, y = x[..., :3], y[..., :3]
+        assert x.tobytes() == y.tobytes(), f
+
+
+def test_cornell_records_match_reference_host():
+    d = host.load_ptbd(os.path.join(util.GOLDEN, "cornell_96x64.ptbd"))
+    s = host.Scene(ptb=_NoDevice())
+    s.add_Obj(util.CORNELL, (555, 0, 0), (1, 1, 1), 0, 0)       # main.cpp:552-617
+    s._flush()
+    fields_equal(s.tris, d["tris"], ["r1", "r2", "r3", "N", "mati"])
+    fields_equal(np.stack(s.mats), d["mats"], ["kd", "ks", "emission", "F0", "n", "shininess", "type"])
+    fields_equal(host.nodes_to_records(s.kd_tree), d["kd_tree"], ["trii", "bl", "tr"])   # main.cpp:195-304
+    assert s.kd_tree_shift == d["kd_tree_shift"].tolist() == [0, 3, 6]                    # main.cpp:537-540
+    cam = host.camera_at(96, 64, 39.3, 0, 0, (277.5, 277.5, -800))                       # main.cpp:311-347
+    fields_equal(cam.reshape(1), d["camera"].reshape(1), ["eye", "lookat", "up", "right", "XM", "YM"])
+
+
+def test_procedural_scene_records_match_reference_host():
+    d = host.load_ptbd(os.path.join(util.GOLDEN, "small_mixed_80x60.ptbd"))
+    s = host.Scene(ptb=_NoDevice())
+    desc = scenes.describe("small_mixed")
+    scenes.populate(s, desc)                                      # add_Material / add_Triangle / end_Obj
+    s._flush()
+    fields_equal(s.tris, d["tris"], ["r1", "r2", "r3", "N", "mati"])
+    fields_equal(np.stack(s.mats), d["mats"], ["kd", "ks", "emission", "F0", "n", "shininess", "type"])
+    fields_equal(host.nodes_to_records(s.kd_tree), d["kd_tree"], ["trii", "bl", "tr"])
+    assert s.kd_tree_shift == d["kd_tree_shift"].tolist()
+
+
+@pytest.mark.skipif(not util.have_ref_cpu(), reason="oracle/_ref/ref_cpu not built")
+def test_rotated_camera_matches_reference_host():
+    ref = util.run_ref_cpu(40, 30, 0, 4, obj=util.CORNELL, eye=(100.0, 350.0, -600.0), fov=61.5, yaw=-13.8, pitch=15.6, want=("dump",))
+    d = host.load_ptbd(ref["files"]["dump"])
+    cam = host.camera_at(40, 30, 61.5, -13.8, 15.6, (100.0, 350.0, -600.0))
+    fields_equal(cam.reshape(1), d["camera"].reshape(1), ["eye", "lookat", "up", "right", "XM", "YM"])
+
+
+def test_seed_jump_ahead_equals_sequential():
+    x, ref = 1, []
+    for _ in range(20000):
+        x = (x * 16807) % 2147483647
+        ref.append(x)
+    assert (host.minstd_rand0_seeds(20000) == np.asarray(ref, dtype=np.int32)).all()
+    assert (host.minstd_rand0_seeds(777, skip=9000) == np.asarray(ref[9000:9777], dtype=np.int32)).all()
+    assert host.minstd_rand0_seeds(0).size == 0
+
+
+def test_missing_custom_mtl_key_raises(tmp_path):
+    # main.cpp:568-571: unknown_parameter.at("Kn") throws when the custom keys are absent
+    (tmp_path / "a.mtl").write_text("newmtl m\nKd 1 1 1\nKs 0 0 0\nKe 0 0 0\nNs 1\n")
+    (tmp_path / "a.obj").write_text("mtllib a.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nusemtl m\nf 1 2 3\n")
+    with pytest.raises(KeyError):
+        host.load_obj(str(tmp_path / "a.obj"))
+
+
+def test_coincident_centroids_are_rejected():
+    # the reference's builder loops forever on > 6 triangles with identical centroids (main.cpp:246-257)
+    t = host.Triangles(np.zeros((8, 3)), np.tile([1, 0, 0], (8, 1)), np.tile([0, 1, 0], (8, 1)), np.zeros(8))
+    with pytest.raises(ValueError):
+        host.build_object_tree(t, 0, [], 0)
+
+
+def test_scene_generators_are_deterministic_and_sized():
+    a, b = scenes.describe("spheres100k"), scenes.describe("spheres100k")
+    assert a["verts"].tobytes() == b["verts"].tobytes()
+    assert 90_000 <= len(a["verts"]) <= 120_000
+    g = scenes.describe("small_mixed")
+    assert len(g["verts"]) == g["obj_end"][-1] == len(g["tri_mat"])

@@ -1,0 +1,76 @@
+"""N > 1 host logic on CPU: world_size-2 process groups over gloo (the GPU box runs the same code over NCCL).
+The render call itself is stood in by the CPU oracle — only the sharding / seeding / merge logic is under test."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from opencl_path_tracer_b200 import host, multigpu
+from tests import util
+
+W, H, SPP = 48, 32, 3
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _oracle_render(rank_skip, spp):
+    from oracle import pt_oracle_py as po
+    surf = dict(host.load_ptbd(os.path.join(util.GOLDEN, "cornell_96x64.ptbd")))
+    surf["W"], surf["H"] = W, H
+    surf["camera"] = host.camera_at(W, H, 39.3, 0, 0, (277.5, 277.5, -800))
+    o = po.OracleScene(surf, seeds=host.minstd_rand0_seeds(W * H, rank_skip))
+    return o.render(spp, threads=2).reshape(-1, 4).copy()
+
+
+def _worker(rank, world, port, mode, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        if mode == "tile":
+            full = _oracle_render(0, SPP)                            # every rank has the reference's seeds
+            owner = multigpu.pixel_owner(W, H, world, multigpu.shard_group(W, rows=8))
+            local = torch.from_numpy(np.where((owner == rank)[:, None], full, np.float32(0.0)))
+            merged = multigpu.merge_tile_split(local)
+            np.save(os.path.join(out_dir, f"tile_{rank}.npy"), merged.numpy())
+        else:
+            mean = _oracle_render(multigpu.rank_seed_skip(rank, W, H), SPP)
+            buf = torch.from_numpy(mean * np.float32(SPP))           # what the sum-mode kernel leaves in colors[]
+            multigpu.reduce_sum_to_root(buf)
+            if rank == 0:
+                np.save(os.path.join(out_dir, "spp.npy"), multigpu.merge_spp_split(buf, SPP * world).numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("mode", ["tile", "spp"])
+def test_world_size_2_gloo(tmp_path, mode):
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, mode, str(tmp_path)), nprocs=2, join=True)
+    if mode == "tile":
+        full = _oracle_render(0, SPP)
+        for r in range(2):       # tile split is BITWISE the single-rank image, on every rank
+            assert np.load(tmp_path / f"tile_{r}.npy").tobytes() == full.tobytes()
+    else:
+        m0 = _oracle_render(0, SPP)
+        m1 = _oracle_render(multigpu.rank_seed_skip(1, W, H), SPP)
+        want = (m0.astype(np.float64) + m1.astype(np.float64)) / 2
+        got = np.load(tmp_path / "spp.npy")
+        assert np.allclose(got, want, rtol=2e-6, atol=1e-7)
+        assert not np.array_equal(m0, m1)                            # rank 1 really used a different seed set
+
+
+def test_pixel_owner_partitions_the_image():
+    for n in (1, 2, 4, 8):
+        own = multigpu.pixel_owner(1920, 1080, n, multigpu.shard_group(1920, rows=8))
+        counts = np.bincount(own, minlength=n)
+        assert counts.sum() == 1920 * 1080 and counts.min() > 0
+        assert counts.max() - counts.min() <= 1920 * 8               # at most one band of imbalance
+    assert multigpu.rank_seed_skip(3, 1920, 1080) == 3 * 1920 * 1080
