@@ -546,6 +546,9 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
     }
 }
 
+#include "pt_sched.cuh"
+#include "pt_wavefront.cuh"
+
 // gen_ray as its own launch (prog.cl:384-389): only for hosts that drive the reference's two-kernel sequence
 __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n) {
     size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -591,7 +594,13 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
     } else if (p.accel == PT_ACCEL_REFBVH) {
         if (c) launch_one<PT_ACCEL_REFBVH, true, 0>(p, st); else launch_one<PT_ACCEL_REFBVH, false, 0>(p, st);
     } else {
-        if (c) launch_one<PT_ACCEL_LBVH, true, 0>(p, st); else launch_one<PT_ACCEL_LBVH, false, 0>(p, st);
+        static const int sched = getenv("PTB_LBVH_SCHED") ? atoi(getenv("PTB_LBVH_SCHED")) : 1;
+        dim3 grid((p.W + 15) / 16, (p.H + 7) / 8);
+        if (sched == 0) { if (c) launch_one<PT_ACCEL_LBVH, true, 0>(p, st); else launch_one<PT_ACCEL_LBVH, false, 0>(p, st); }
+        else if (c) k_render_sched<true, 1><<<grid, PT_BLOCK, 0, st>>>(p);
+        else if (sched == 2) k_render_sched<false, 6><<<grid, PT_BLOCK, 0, st>>>(p);
+        else if (sched == 3) k_render_sched<false, 8><<<grid, PT_BLOCK, 0, st>>>(p);
+        else k_render_sched<false, 1><<<grid, PT_BLOCK, 0, st>>>(p);
     }
 }
 

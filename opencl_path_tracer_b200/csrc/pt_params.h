@@ -53,16 +53,23 @@ struct RenderParams {
     int accel;                    // PT_ACCEL_*
     int count_work;               // 1: also count box / triangle tests
     unsigned long long *counters; // PT_CNT_WORDS words
+    // wavefront pipeline scratch (pt_wavefront.cuh), one path per pixel, allocated by ptb_abi.cu; null = megakernel only
+    float4 *wf_ray0, *wf_ray1;    // (P.xyz, D.x) (D.y, D.z, t_hit, bits(tri))
+    float4 *wf_state;             // 6 planes of W*H float4: throughputs, sample colour, accumulator, rng, counters
+    int *wf_queue[2];             // active pixel ids, double buffered
+    int *wf_ctrl;                 // [0],[1] queue lengths, [2] fetch cursor of the trace kernel, [3] spare
 };
 
 // one entry per translation unit; implemented in pt_kernels.cuh
 namespace pt_parity {
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
+int launch_wavefront(const RenderParams &p, cudaStream_t s);   // returns the number of kernels launched
 }
 namespace pt_fast {
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
+int launch_wavefront(const RenderParams &p, cudaStream_t s);
 }
 
 #endif  // PT_PARAMS_H_

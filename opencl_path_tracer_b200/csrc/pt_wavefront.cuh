@@ -1,0 +1,296 @@
+// pt_wavefront.cuh — wavefront organisation of the same path (included inside namespace PT_NS).
+//
+// One PATH per pixel lives in global memory (ray 32 B + state 96 B).  A render is a sequence of
+// iterations; each iteration advances every active path by one ray:
+//     k_wf_trace   persistent warps; every lane pulls the next queued path as soon as its traversal
+//                  ends (warp-aggregated atomic fetch), so no lane waits for a neighbour's long
+//                  traversal; inside, box steps and leaf steps are phase-scheduled by warp votes
+//     k_wf_shade   one thread per queued path, full warps: hit → material → bounce sampling →
+//                  throughput update (prog.cl:321-366), path end → running mean (prog.cl:379) and the
+//                  NEXT sample's camera ray (prog.cl:384-389) in the same thread; surviving paths are
+//                  appended to the next queue with a warp ballot + one atomic per warp
+// A pixel's samples stay strictly sequential (same RNG order as the megakernel and the reference),
+// so the result is bit-identical to the other pipelines in the parity flavour.
+// Iterations needed: at most spp * iterations (every active path consumes one ray per iteration).
+
+#define WF_PLANES 6
+struct WfPath {
+    Path ps;
+    V3 acc;
+    uint32_t rng;
+    int s, depth;
+};
+PT_DEV void wf_store_state(const RenderParams &p, int i, const WfPath &w) {
+    const size_t n = (size_t)p.W * p.H;
+    float4 *st = p.wf_state + i;
+    st[0 * n] = make_float4(w.ps.fL.x, w.ps.fL.y, w.ps.fL.z, w.ps.fB.x);
+    st[1 * n] = make_float4(w.ps.fB.y, w.ps.fB.z, w.ps.fS.x, w.ps.fS.y);
+    st[2 * n] = make_float4(w.ps.fS.z, w.ps.fR.x, w.ps.fR.y, w.ps.fR.z);
+    st[3 * n] = make_float4(w.ps.color.x, w.ps.color.y, w.ps.color.z, __uint_as_float(w.rng));
+    st[4 * n] = make_float4(w.acc.x, w.acc.y, w.acc.z, __int_as_float(w.s));
+    st[5 * n] = make_float4(__int_as_float(w.depth), __int_as_float(w.ps.in ? 1 : 0), 0.0f, 0.0f);
+}
+PT_DEV void wf_load_state(const RenderParams &p, int i, WfPath &w) {
+    const size_t n = (size_t)p.W * p.H;
+    const float4 *st = p.wf_state + i;
+    const float4 a = st[0 * n], b = st[1 * n], c = st[2 * n], d = st[3 * n], e = st[4 * n], f = st[5 * n];
+    w.ps.fL = v3(a.x, a.y, a.z); w.ps.fB = v3(a.w, b.x, b.y); w.ps.fS = v3(b.z, b.w, c.x); w.ps.fR = v3(c.y, c.z, c.w);
+    w.ps.color = v3(d.x, d.y, d.z); w.rng = __float_as_uint(d.w);
+    w.acc = v3(e.x, e.y, e.z); w.s = __float_as_int(e.w);
+    w.depth = __float_as_int(f.x); w.ps.in = __float_as_int(f.y) != 0;
+}
+PT_DEV void wf_store_ray(const RenderParams &p, int i, V3 P, V3 D) {
+    p.wf_ray0[i] = make_float4(P.x, P.y, P.z, D.x);
+    p.wf_ray1[i] = make_float4(D.y, D.z, PT_NO_HIT, __int_as_float(0x7fffffff));
+}
+
+// append `i` to the output queue for the lanes with keep == true: one atomic per warp
+PT_DEV void wf_push(int *queue, int *count, bool keep, int i) {
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == (__ffs(m) - 1)) base = atomicAdd(count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (keep) queue[base + __popc(m & ((1u << lane) - 1u))] = i;
+}
+
+// starts the next sample(s) of pixel i until a path is in flight or all samples are done; returns alive
+PT_DEV bool wf_next_sample(const RenderParams &p, int i, WfPath &w, V3 &rayP, V3 &rayD, int s_end, Work &wk) {
+    const int camX = (int)p.cam.XM;
+    while (w.s < s_end) {
+        float r1 = pt_rand(w.rng), r2 = pt_rand(w.rng);
+        camera_get_ray_xy(i % max(camX, 1), i / max(camX, 1), p.cam, r1, r2, rayP, rayD);
+        path_reset(w.ps);
+        w.depth = 0;
+        if (p.iterations > 0) return true;
+        if (p.sum_mode) w.acc = w.acc + w.ps.color; else w.acc = pt_mean_step(w.acc, w.ps.color, w.s);
+        ++w.s;
+        wk.samples++;
+    }
+    return false;
+}
+PT_DEV void wf_finish_pixel(const RenderParams &p, int i, const WfPath &w) {
+    p.rnds[i] = (int)w.rng;
+    p.colors[i] = make_float4(w.acc.x, w.acc.y, w.acc.z, 0.0f);
+    if (p.tex) p.tex[i] = reinhard_tone_map(w.acc);
+}
+PT_DEV void wf_flush_counters(const RenderParams &p, const Work &wk, bool count) {
+    if (!p.counters) return;
+    const int lane = threadIdx.x & 31;
+    unsigned v[7] = {wk.rays, wk.box, wk.tri, wk.tri1, wk.tri2, wk.tri3, wk.samples};
+    const int idx[7] = {PT_CNT_RAYS, PT_CNT_BOX, PT_CNT_TRI, PT_CNT_TRI1, PT_CNT_TRI2, PT_CNT_TRI3, PT_CNT_PIXEL_SAMPLES};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        if (!count && k >= 1 && k <= 5) continue;
+        unsigned long long tot = v[k];
+        for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        if (lane == 0 && tot) atomicAdd(p.counters + idx[k], tot);
+    }
+}
+
+// ---------------------------------------------------------------- init: first camera ray of every selected pixel
+__global__ void __launch_bounds__(256) k_wf_init(const RenderParams p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = p.W * p.H;
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    bool keep = false;
+    if (i < n && (p.shard_n <= 1 || ((i / p.shard_group) % p.shard_n) == p.shard_rank)) {
+        WfPath w;
+        w.rng = (uint32_t)p.rnds[i];
+        w.acc = (p.sample0 != 0 || p.sum_mode) ? v3(p.colors[i]) : v3(0.0f, 0.0f, 0.0f);
+        w.s = p.sample0;
+        w.depth = 0;
+        path_reset(w.ps);
+        V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
+        keep = wf_next_sample(p, i, w, P, D, p.sample0 + p.spp, wk);
+        if (keep) { wf_store_ray(p, i, P, D); wf_store_state(p, i, w); }
+        else wf_finish_pixel(p, i, w);
+    }
+    wf_push(p.wf_queue[0], p.wf_ctrl + 0, keep, i);
+    wf_flush_counters(p, wk, false);
+}
+
+// ---------------------------------------------------------------- shade: one thread per queued path
+// q_in/n_in: this iteration's queue; survivors go to q_out/n_out (zeroed by the host before the launch)
+__global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const int *q_in, const int *n_in, int *q_out, int *n_out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int count = *n_in;
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    bool keep = false;
+    int i = 0;
+    if (j < count) {
+        i = q_in[j];
+        const SceneDev &sc = p.sc;
+        const float4 r0 = p.wf_ray0[i], r1 = p.wf_ray1[i];
+        V3 rayP = v3(r0.x, r0.y, r0.z), rayD = v3(r0.w, r1.x, r1.y);
+        const float t = r1.z;
+        const int tri = __float_as_int(r1.w);
+        WfPath w;
+        wf_load_state(p, i, w);
+        const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
+        bool alive = true;
+        wk.rays++;
+        if (t < PT_NO_HIT) {
+            V3 hitP = rayP + rayD * t;                               // prog.cl:107
+            V3 hitN = tri_normal(ldg4(sc.q0 + tri), ldg4(sc.q1 + tri), ldg4(sc.q2 + tri));
+            Mat m = load_material(sc.mats, (int)__ldg(sc.mati + tri));
+            shade_hit(m, hitP, hitN, rayP, rayD, w.rng, w.ps, eye, p.iterations);
+            if (++w.depth >= p.iterations) alive = false;
+        } else {
+            alive = false;                                           // miss: break, prog.cl:367-376
+        }
+        if (!alive) {                                                // sample finished, prog.cl:379
+            if (p.sum_mode) w.acc = w.acc + w.ps.color; else w.acc = pt_mean_step(w.acc, w.ps.color, w.s);
+            ++w.s;
+            wk.samples++;
+            alive = wf_next_sample(p, i, w, rayP, rayD, p.sample0 + p.spp, wk);
+        }
+        if (alive) { wf_store_ray(p, i, rayP, rayD); wf_store_state(p, i, w); }
+        else wf_finish_pixel(p, i, w);
+        keep = alive;
+    }
+    wf_push(q_out, n_out, keep, i);
+    wf_flush_counters(p, wk, false);
+}
+
+// ---------------------------------------------------------------- trace: persistent warps over the queue
+enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3 };
+#ifndef WF_FETCH_MIN
+#define WF_FETCH_MIN 8            // refill when this many lanes are idle (or nothing else is runnable)
+#endif
+#define WF_SMEM_STACK 16
+
+template <bool COUNT>
+__global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor) {
+    const SceneDev &sc = p.sc;
+    const int lane = threadIdx.x & 31;
+    const int count = *n_in;
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    __shared__ int2 s_stack[WF_SMEM_STACK * PT_BLOCK];
+    int2 *my_stack = s_stack + threadIdx.x;
+    int2 deep_stack[PT_LBVH_STACK - WF_SMEM_STACK];
+    int st = WF_FETCH, link = 0, sp = 0, path = 0;
+    bool exhausted = count == 0;
+    V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
+    Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+    float ix = 0.0f, iy = 0.0f, iz = 0.0f, ox = 0.0f, oy = 0.0f, oz = 0.0f;
+#define WF_PUSH(v, d) do { const int2 e_ = make_int2((v), __float_as_int(d)); if (sp < WF_SMEM_STACK) my_stack[sp * PT_BLOCK] = e_; \
+                           else if (sp < PT_LBVH_STACK) deep_stack[sp - WF_SMEM_STACK] = e_; ++sp; } while (0)
+#define WF_POP_LIVE(ok) do { ok = false; while (sp > 0) { --sp; const int2 e_ = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK]; \
+                             if (__int_as_float(e_.y) <= best.t) { link = e_.x; ok = true; break; } } } while (0)
+#define WF_FINISH() do { float4 *o_ = p.wf_ray1 + path; o_->z = best.t; o_->w = __int_as_float(best.tri); st = WF_FETCH; } while (0)
+    for (;;) {
+        if (exhausted && st == WF_FETCH) st = WF_EXIT;
+        const unsigned bF = __ballot_sync(0xffffffffu, st == WF_FETCH);
+        const unsigned bN = __ballot_sync(0xffffffffu, st == WF_NODE);
+        const unsigned bL = __ballot_sync(0xffffffffu, st == WF_LEAF);
+        if ((bF | bN | bL) == 0u) break;
+        const int cF = __popc(bF), cN = __popc(bN), cL = __popc(bL);
+        if (cF > 0 && (cF >= WF_FETCH_MIN || (bN | bL) == 0u)) {
+            // ------------------------------------------------------------ FETCH: one atomic for the whole warp
+            int base = 0;
+            if (lane == (__ffs(bF) - 1)) base = atomicAdd(cursor, cF);
+            base = __shfl_sync(0xffffffffu, base, __ffs(bF) - 1);
+            if (base + cF >= count) exhausted = true;
+            if (st == WF_FETCH) {
+                const int j = base + __popc(bF & ((1u << lane) - 1u));
+                if (j < count) {
+                    path = q_in[j];
+                    const float4 r0 = p.wf_ray0[path], r1 = p.wf_ray1[path];
+                    P = v3(r0.x, r0.y, r0.z); D = v3(r0.w, r1.x, r1.y);
+                    ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
+                    ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
+                    best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+                    sp = 0;
+                    link = sc.bvh_root;
+                    st = link >= 0 ? WF_NODE : WF_LEAF;
+                } else {
+                    st = WF_EXIT;
+                }
+            }
+        } else if (cN >= cL) {
+            // ------------------------------------------------------------ NODE steps
+#pragma unroll 1
+            for (int k = 0; k < PT_SCHED_NODE_STEPS; ++k) {
+                if (st == WF_NODE) {
+                    const float4 *nd = sc.bvh + 4 * (size_t)link;
+                    const float4 n0 = ldg4(nd), n1 = ldg4(nd + 1), n2 = ldg4(nd + 2), n3 = ldg4(nd + 3);
+                    if (COUNT) wk.box += 2;
+                    float a, b, l0, l1, r0, r1;
+                    a = fmaf(n0.x, ix, -ox); b = fmaf(n0.y, ix, -ox); l0 = fminf(a, b); l1 = fmaxf(a, b);
+                    a = fmaf(n0.z, iy, -oy); b = fmaf(n0.w, iy, -oy); l0 = fmaxf(l0, fminf(a, b)); l1 = fminf(l1, fmaxf(a, b));
+                    a = fmaf(n2.x, iz, -oz); b = fmaf(n2.y, iz, -oz); l0 = fmaxf(l0, fminf(a, b)); l1 = fminf(l1, fmaxf(a, b));
+                    a = fmaf(n1.x, ix, -ox); b = fmaf(n1.y, ix, -ox); r0 = fminf(a, b); r1 = fmaxf(a, b);
+                    a = fmaf(n1.z, iy, -oy); b = fmaf(n1.w, iy, -oy); r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
+                    a = fmaf(n2.z, iz, -oz); b = fmaf(n2.w, iz, -oz); r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
+                    const bool hl = (l0 <= l1 * 1.000004f) & (l1 >= 0.0f) & (l0 * 0.999996f <= best.t);
+                    const bool hr = (r0 <= r1 * 1.000004f) & (r1 >= 0.0f) & (r0 * 0.999996f <= best.t);
+                    const int ll = __float_as_int(n3.x), lr = __float_as_int(n3.y);
+                    if (hl & hr) {
+                        const bool left_first = l0 <= r0;
+                        WF_PUSH(left_first ? lr : ll, (left_first ? r0 : l0) * 0.999996f);
+                        link = left_first ? ll : lr;
+                    } else if (hl | hr) {
+                        link = hl ? ll : lr;
+                    } else {
+                        bool ok;
+                        WF_POP_LIVE(ok);
+                        if (!ok) WF_FINISH();
+                    }
+                    if (st == WF_NODE && link < 0) st = WF_LEAF;
+                }
+            }
+        } else {
+            // ------------------------------------------------------------ LEAF step
+            if (st == WF_LEAF) {
+                const int enc = ~link;
+                const int first = enc >> 3, cnt = (enc & 7) + 1;
+                for (int k = 0; k < cnt; ++k) {
+                    const int pos = first + k;
+                    float t;
+                    const bool acc_ = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
+                    if (acc_ & (t > 0.0f) & (t <= best.t)) {
+                        const int tid = __ldg(sc.sorted_id + pos);
+                        if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
+                    }
+                }
+                bool ok;
+                WF_POP_LIVE(ok);
+                if (!ok) WF_FINISH(); else st = link >= 0 ? WF_NODE : WF_LEAF;
+            }
+        }
+    }
+    wf_flush_counters(p, wk, COUNT);
+}
+
+// ---------------------------------------------------------------- host side: the iteration loop
+int launch_wavefront(const RenderParams &p, cudaStream_t st) {
+    const int n = p.W * p.H;
+    int launches = 0;
+    cudaMemsetAsync(p.wf_ctrl, 0, 4 * sizeof(int), st);
+    k_wf_init<<<(n + 255) / 256, 256, 0, st>>>(p);
+    ++launches;
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int trace_blocks = sms * 6;
+    const long long max_iters = (long long)p.spp * (p.iterations > 0 ? p.iterations : 0);
+    int host_count = n;
+    for (long long it = 0; it < max_iters; ++it) {
+        const int a = (int)(it & 1), b = a ^ 1;
+        // next queue length and the fetch cursor start at zero
+        cudaMemsetAsync(p.wf_ctrl + b, 0, sizeof(int), st);
+        cudaMemsetAsync(p.wf_ctrl + 2, 0, sizeof(int), st);
+        if (p.count_work) k_wf_trace<true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2);
+        else k_wf_trace<false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2);
+        k_wf_shade<<<(host_count + 255) / 256, 256, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_queue[b], p.wf_ctrl + b);
+        launches += 2;
+        if ((it & 15) == 15) {                     // every 16 iterations: learn the real queue length (shrinks the grids, ends early)
+            cudaMemcpyAsync(&host_count, p.wf_ctrl + b, sizeof(int), cudaMemcpyDeviceToHost, st);
+            cudaStreamSynchronize(st);
+            if (host_count == 0) break;
+        }
+    }
+    return launches;
+}

@@ -78,6 +78,8 @@ struct State {
     unsigned long long launches = 0;
     Staged staged;
     PendingGen pending;
+    void *wf_blob = nullptr;           // wavefront scratch (ray + path state + queues), grown on demand
+    size_t wf_pixels = 0;
 };
 // immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
 // during static destruction, after which ptb_release still gets called
@@ -291,6 +293,28 @@ int run_render(const RenderParams &p) {
     return PTB_SUCCESS;
 }
 
+// wavefront pipeline: 136 bytes of scratch per pixel (ray 32, path state 96, two queue slots 8)
+int run_wavefront(RenderParams &p) {
+    const size_t n = (size_t)p.W * p.H;
+    if (n > G.wf_pixels) {
+        cudaFree(G.wf_blob);
+        G.wf_blob = nullptr; G.wf_pixels = 0;
+        CUDA_OK(cudaMalloc(&G.wf_blob, n * 136 + 256));
+        G.wf_pixels = n;
+    }
+    char *b = (char *)G.wf_blob;
+    p.wf_ray0 = (float4 *)b; b += n * 16;
+    p.wf_ray1 = (float4 *)b; b += n * 16;
+    p.wf_state = (float4 *)b; b += n * 96;
+    p.wf_queue[0] = (int *)b; b += n * 4;
+    p.wf_queue[1] = (int *)b; b += n * 4;
+    p.wf_ctrl = (int *)b;
+    int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_wavefront(p, G.stream) : pt_fast::launch_wavefront(p, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches += (unsigned long long)k;
+    return PTB_SUCCESS;
+}
+
 }  // namespace
 
 extern "C" {
@@ -337,6 +361,8 @@ int ptb_shutdown(void) {
     s = Staged();
     cudaFree(G.counters);
     G.counters = nullptr;
+    cudaFree(G.wf_blob);
+    G.wf_blob = nullptr; G.wf_pixels = 0;
     cudaStreamDestroy(G.own_stream);
     G.own_stream = G.stream = nullptr;
     for (auto &k : G.args) for (auto &a : k) a = Arg();
@@ -597,6 +623,7 @@ int ptb_render(int spp) {
     RenderParams p;
     rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
     if (rc) return rc;
+    if (G.pipe == PTB_PIPE_WAVEFRONT && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);   // tiny scenes: the megakernel's shared-memory scan
     return run_render(p);
 }
 

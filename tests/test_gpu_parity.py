@@ -159,3 +159,17 @@ def test_reference_host_over_cuda_shim(tmp_path):
     st = util.compare(colors, ref["colors"])
     assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
     assert info["rays"] == ref["info"]["rays"]
+
+
+# ---------------------------------------------------------------- wavefront pipeline == megakernel == oracle
+@pytest.mark.parametrize("which", ["mixed", "spheres"])
+def test_wavefront_parity(ptb, mixed_ref, spheres_ref, which):
+    ref, spp = (mixed_ref, 8) if which == "mixed" else (spheres_ref, 4)
+    ptb.set_pipeline(capi.PIPE_WAVEFRONT)
+    try:
+        colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp)
+    finally:
+        ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    st = util.compare(colors, ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+    assert (rnds == ref["rnds"]).mean() >= 1.0 - 1e-4
