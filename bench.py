@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--math", default="fast", choices=["fast", "parity"])
     ap.add_argument("--accel", default="auto", choices=["auto", "brute", "refbvh", "lbvh"])
-    ap.add_argument("--pipeline", default="megakernel", choices=["megakernel", "wavefront"])
+    ap.add_argument("--pipeline", default="auto", choices=["auto", "megakernel", "wavefront"])
     ap.add_argument("--ref-spp", type=int, default=0, help="reference arm: samples per step (default: sized to a few seconds)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -191,7 +191,7 @@ def main():
     ptb.set_stream(stream.cuda_stream)
     ptb.set_math(capi.MATH_FAST if args.math == "fast" else capi.MATH_PARITY)
     ptb.set_accel({"auto": 0, "brute": 1, "refbvh": 2, "lbvh": 3}[args.accel])
-    ptb.set_pipeline(capi.PIPE_WAVEFRONT if args.pipeline == "wavefront" else capi.PIPE_MEGAKERNEL)
+    ptb.set_pipeline({"auto": capi.PIPE_AUTO, "megakernel": capi.PIPE_MEGAKERNEL, "wavefront": capi.PIPE_WAVEFRONT}[args.pipeline])
 
     scene = host.Scene(ptb)
     scene.build_trees = args.accel == "refbvh"

@@ -100,7 +100,9 @@ enum {
 /* Kernel organisation of ptb_render. */
 enum {
     PTB_PIPE_MEGAKERNEL = 0,   /* one persistent kernel, path regeneration inside the loop              */
-    PTB_PIPE_WAVEFRONT = 1     /* generate / intersect / shade kernels over compacted ray queues        */
+    PTB_PIPE_WAVEFRONT = 1,    /* generate / intersect / shade kernels over compacted ray queues        */
+    PTB_PIPE_AUTO = 2          /* default — the faster one by measurement: megakernel for the
+                                  shared-memory brute force, wavefront for the LBVH                         */
 };
 int ptb_set_accel(int accel);
 int ptb_set_math(int math);

@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 KERNEL_GEN_RAY, KERNEL_TRACE_RAY, KERNEL_FILT_IM = 0, 1, 2
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_REFBVH, ACCEL_LBVH = 0, 1, 2, 3
 MATH_PARITY, MATH_FAST = 0, 1
-PIPE_MEGAKERNEL, PIPE_WAVEFRONT = 0, 1
+PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO = 0, 1, 2
 
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py against the header text)
 SYMBOLS = [

@@ -68,7 +68,7 @@ struct State {
     ptb_mem next = 1;
     Arg args[PTB_KERNEL_COUNT][16];
     std::string err;
-    int accel = PTB_ACCEL_AUTO, math = PTB_MATH_FAST, pipe = PTB_PIPE_MEGAKERNEL;
+    int accel = PTB_ACCEL_AUTO, math = PTB_MATH_FAST, pipe = PTB_PIPE_AUTO;
     int fuse_gen = 1;
     int shard_rank = 0, shard_n = 1, shard_group = 1;
     int sum_mode = 0, count_work = 0;
@@ -572,7 +572,7 @@ int ptb_set_math(int math) {
     return PTB_SUCCESS;
 }
 int ptb_set_pipeline(int pipe) {
-    if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT) return PTB_ERR_INVALID_VALUE;
+    if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT && pipe != PTB_PIPE_AUTO) return PTB_ERR_INVALID_VALUE;
     G.pipe = pipe;
     return PTB_SUCCESS;
 }
@@ -623,7 +623,7 @@ int ptb_render(int spp) {
     RenderParams p;
     rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
     if (rc) return rc;
-    if (G.pipe == PTB_PIPE_WAVEFRONT && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);   // tiny scenes: the megakernel's shared-memory scan
+    if (G.pipe != PTB_PIPE_MEGAKERNEL && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);   // tiny scenes: the megakernel's shared-memory scan
     return run_render(p);
 }
 

@@ -26,10 +26,12 @@ def cornell_ref():
     return util.run_ref_cpu(W, H, SPP, DEPTH, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3)
 
 
-def render(ptb, ref, accel, math, mode, spp=SPP):
+def render(ptb, ref, accel, math, mode, spp=SPP, pipeline=capi.PIPE_MEGAKERNEL):
     surf = host.load_ptbd(ref["files"]["dump"])
     ptb.set_accel(accel)
     ptb.set_math(math)
+    if pipeline is not None:
+        ptb.set_pipeline(pipeline)
     s = host.scene_from_surface(surf, ptb)
     if mode == "two_kernel":          # literal gen_ray + trace_ray launches per sample, unfused
         ptb.set_fuse_gen(0)
@@ -165,11 +167,7 @@ def test_reference_host_over_cuda_shim(tmp_path):
 @pytest.mark.parametrize("which", ["mixed", "spheres"])
 def test_wavefront_parity(ptb, mixed_ref, spheres_ref, which):
     ref, spp = (mixed_ref, 8) if which == "mixed" else (spheres_ref, 4)
-    ptb.set_pipeline(capi.PIPE_WAVEFRONT)
-    try:
-        colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp)
-    finally:
-        ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp, pipeline=capi.PIPE_WAVEFRONT)
     st = util.compare(colors, ref["colors"])
     assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
     assert (rnds == ref["rnds"]).mean() >= 1.0 - 1e-4
