@@ -34,6 +34,11 @@ struct SceneDev {
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
+    // merged scan primitives for the fast brute-force scan (prims.cu); n_prims == 0: not built / nothing merged
+    const float4 *pq0, *pq1, *pq2;// fast layout
+    const float *prim_f;          // 1: parallelogram of two triangles, 0: lone triangle
+    const int *prim_rep;          // primitive → upload index of the triangle that stands for it
+    int n_prims;
 };
 
 struct RenderParams {

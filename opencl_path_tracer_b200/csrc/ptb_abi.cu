@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "lbvh.h"
+#include "prims.h"
 #include "pt_params.h"
 #include "ptb200.h"
 #include "resolve.h"
@@ -50,6 +51,12 @@ struct Staged {                        // device-internal copy of the scene, val
     Lbvh lbvh;
     bool lbvh_valid = false;
     int lbvh_leaf = 0;
+    // merged scan primitives (prims.cu), built on first use by a fast brute-force launch
+    float4 *p0 = nullptr, *p1 = nullptr, *p2 = nullptr;
+    float *prim_f = nullptr;
+    int *prim_rep = nullptr, *n_prims_dev = nullptr;
+    int n_prims = 0;
+    bool prims_valid = false;
 };
 
 struct PendingGen {                    // a deferred gen_ray launch (ptb_set_fuse_gen)
@@ -73,6 +80,7 @@ struct State {
     int shard_rank = 0, shard_n = 1, shard_group = 1;
     int sum_mode = 0, count_work = 0;
     int lbvh_leaf = 4;
+    int merge_prims = 1;
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
     unsigned long long *counters = nullptr;
     unsigned long long launches = 0;
@@ -174,6 +182,33 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
     s.tris_version = tris->version;
     s.n_tris = n_tris;
     s.lbvh_valid = false;
+    s.prims_valid = false;
+    return PTB_SUCCESS;
+}
+
+// Merge coplanar same-material triangle pairs into parallelograms for the fast shared-memory scan (prims.cu).
+// Leaves n_prims = 0 when nothing merges, so the launch keeps the plain triangle scan.
+int ensure_prims() {
+    Staged &s = G.staged;
+    if (s.prims_valid) return PTB_SUCCESS;
+    s.n_prims = 0;
+    s.prims_valid = true;
+    if (!G.merge_prims || s.n_tris < 2 || s.n_tris > PRIMS_MAX_TRIS) return PTB_SUCCESS;
+    if (!s.p0) {
+        CUDA_OK(cudaMalloc((void **)&s.p0, PRIMS_MAX_TRIS * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.p1, PRIMS_MAX_TRIS * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.p2, PRIMS_MAX_TRIS * sizeof(float4)));
+        CUDA_OK(cudaMalloc((void **)&s.prim_f, PRIMS_MAX_TRIS * sizeof(float)));
+        CUDA_OK(cudaMalloc((void **)&s.prim_rep, PRIMS_MAX_TRIS * sizeof(int)));
+        CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
+    }
+    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_f, s.prim_rep, s.n_prims_dev, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches++;
+    int n = 0;
+    CUDA_OK(cudaMemcpyAsync(&n, s.n_prims_dev, sizeof n, cudaMemcpyDeviceToHost, G.stream));
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    if (n > 0 && n < s.n_tris) s.n_prims = n;
     return PTB_SUCCESS;
 }
 
@@ -233,6 +268,11 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.accel = resolve_accel(tris_size, have_tree);
     const bool fastm = G.math == PTB_MATH_FAST;   // each arithmetic flavour reads its own triangle layout
     p.sc.q0 = fastm ? s.f0 : s.q0; p.sc.q1 = fastm ? s.f1 : s.q1; p.sc.q2 = fastm ? s.f2 : s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
+    if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
+        rc = ensure_prims();
+        if (rc) return rc;
+        p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_f = s.prim_f; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
+    }
     p.sc.mats = (const RefMaterial *)mats->dptr;
     p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
     if (have_tree) {
@@ -345,6 +385,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_ACCEL"))) G.accel = atoi(env);
     if ((env = getenv("PTB_LBVH_LEAF"))) G.lbvh_leaf = atoi(env);
     if ((env = getenv("PTB_BRUTE_MAX"))) G.brute_max = atoi(env);
+    if ((env = getenv("PTB_MERGE_PRIMS"))) G.merge_prims = atoi(env) ? 1 : 0;
     return PTB_SUCCESS;
 }
 
@@ -357,6 +398,7 @@ int ptb_shutdown(void) {
     G.mems.clear();
     Staged &s = G.staged;
     cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
+    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_f); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
     lbvh_free(&s.lbvh);
     s = Staged();
     cudaFree(G.counters);
@@ -581,6 +623,12 @@ int ptb_set_fuse_gen(int on) {
     G.fuse_gen = on ? 1 : 0;
     return rc;
 }
+int ptb_set_merge_prims(int on) {
+    G.merge_prims = on ? 1 : 0;
+    G.staged.prims_valid = false;
+    return PTB_SUCCESS;
+}
+int ptb_scan_prims(void) { return G.staged.prims_valid && G.staged.n_prims > 0 ? G.staged.n_prims : (G.staged.n_tris > 0 ? G.staged.n_tris : 0); }
 int ptb_set_lbvh_leaf(int max_tris) {
     if (max_tris < 1 || max_tris > 8) return PTB_ERR_INVALID_VALUE;
     G.lbvh_leaf = max_tris;

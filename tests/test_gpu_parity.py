@@ -65,6 +65,26 @@ def test_fast_math_within_tolerance(ptb, cornell_ref, accel):
     assert st["rmse_over_mean"] <= 0.01, st
 
 
+def test_merged_parallelograms_match_triangle_scan(ptb, cornell_ref):
+    """Fast brute-force scan over merged primitives (prims.cu) vs. the same scan over the plain triangles:
+    the Cornell box's fan-triangulated quads must merge, and the image must stay within the fast tolerance."""
+    try:
+        ptb.set_merge_prims(0)
+        plain, _ = render(ptb, cornell_ref, capi.ACCEL_BRUTE, capi.MATH_FAST, "render_spp")
+        n_plain = ptb.scan_prims()
+        ptb.set_merge_prims(1)
+        merged, _ = render(ptb, cornell_ref, capi.ACCEL_BRUTE, capi.MATH_FAST, "render_spp")
+        n_merged = ptb.scan_prims()
+    finally:
+        ptb.set_merge_prims(1)
+    assert n_plain == cornell_ref["info"]["n_tris"] if "n_tris" in cornell_ref["info"] else n_plain > 0
+    assert n_merged < n_plain and 2 * n_merged >= n_plain, (n_merged, n_plain)
+    st = util.compare(merged, plain)
+    assert st["frac_rel_le_1e-4"] >= 0.999, st
+    st = util.compare(merged, cornell_ref["colors"])
+    assert st["frac_rel_le_1e-4"] >= 0.999 and st["rmse_over_mean"] <= 0.01, st
+
+
 def test_depth1_preview_is_exact(ptb):
     """iterations == 1: flat kd+emission preview (prog.cl:323-325) — a sharp test of ray generation + closest hit."""
     if not util.have_ref_cpu():
