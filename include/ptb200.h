@@ -115,7 +115,7 @@ int ptb_set_pipeline(int pipe);
  * kernels literally.  Results are identical either way. */
 int ptb_set_fuse_gen(int on);
 int ptb_set_lbvh_leaf(int max_tris); /* 1..8 triangles per LBVH leaf (default 4); takes effect at the next build */
-/* Fast flavour, brute-force scan only: merge coplanar same-material triangle pairs that form a parallelogram
+/* Fast flavour, brute-force scan only: merge coplanar same-material triangle pairs that form a convex quad
  * (a fan-triangulated quad, main.cpp:558) into one scan primitive (default 1).  Never used by PTB_MATH_PARITY. */
 int ptb_set_merge_prims(int on);
 int ptb_scan_prims(void);      /* primitives the last fast brute-force launch scanned (== triangle count when nothing merged) */

@@ -1,20 +1,20 @@
 // prims.cu — primitive merging for the shared-memory brute-force scan (fast flavour only).
 //
 // Meshes authored with quads reach the reference as fan-triangulated pairs (tiny_obj_loader
-// triangulates, main.cpp:558).  Two triangles that share an edge, lie in one plane and together
-// form a PARALLELOGRAM can be tested as one primitive at the cost of one triangle:
-// with the shared edge as the diagonal a1–a3 of triangle A = (a1, a2, a3) and A's barycentric
-// coordinates (u along a2-a1, v along a3-a1) of the plane hit point,
-//     A      : u >= 0, v >= 0, u+v <= 1
-//     B      : u <= 0, u+v >= 0, v <= 1            (B's far corner is a1 + a3 - a2 = (u,v) = (-1,1))
-//     A or B : 0 <= u+v <= 1  and  0 <= v <= 1
-// Only pairs with the same material are merged, and their normals agree, so the shading never needs to
-// know which half was hit: the lower upload index stands for both.
-// A lone triangle is the same test with the u+v >= 0 bound replaced by u >= 0, so one scalar
-// f in {0,1} per primitive selects between them:  k = min(v, 1-v, 1-(u+v), u + f*v) >= 0.
-// The Cornell box (32 triangles = 16 quads) halves its scan this way.  Only exact (bitwise) shared
-// vertices are matched; the plane / parallelogram conditions use a 1e-5 relative tolerance, which
-// is inside the stated tolerance of the fast flavour.  The parity flavour never uses primitives.
+// triangulates, main.cpp:558).  Two triangles that share an edge, lie in one plane, carry the same
+// material and together form a CONVEX QUAD can be tested as one primitive at the cost of one triangle.
+// Anchor the barycentric frame at z, the corner of triangle A opposite the shared edge x–y:
+// u runs along y-z, v along x-z, so y = (1,0), x = (0,1) and B's far corner d = (du,dv).  Then
+//     triangle A   : u >= 0, v >= 0, 1 - u - v >= 0
+//     convex quad  : u >= 0, v >= 0, 1 - u - b*v >= 0 (edge y–d), 1 - v - a*u >= 0 (edge x–d)
+// with b = (1-du)/dv and a = (1-dv)/du; a lone triangle is the same test with b = 1, a = 0 (the fourth
+// bound is then implied).  Two scalars per primitive select the shape:
+//     inside  <=>  min(u, v, 1 - u - b*v, 1 - v - a*u) >= 0.
+// The pair's normals agree and so do their materials, so shading never needs to know which half was
+// hit: the lower upload index stands for both.  The Cornell box (32 triangles = 16 quads, none of the
+// walls an exact parallelogram) halves its scan this way.  Only exact (bitwise) shared vertices are
+// matched; coplanarity / normal agreement use a 1e-5 relative tolerance, inside the stated tolerance
+// of the fast flavour.  The parity flavour never uses primitives.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -25,7 +25,6 @@ namespace {
 struct D3 { double x, y, z; };
 __device__ D3 d3(float4 q) { D3 r = {q.x, q.y, q.z}; return r; }
 __device__ D3 sub(D3 a, D3 b) { D3 r = {a.x - b.x, a.y - b.y, a.z - b.z}; return r; }
-__device__ D3 add(D3 a, D3 b) { D3 r = {a.x + b.x, a.y + b.y, a.z + b.z}; return r; }
 __device__ double dotd(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ D3 crossd(D3 a, D3 b) { D3 r = {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; return r; }
 __device__ bool same(float4 a, float4 b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
@@ -36,39 +35,44 @@ __device__ void load_tri(const float4 *q0, const float4 *q1, const float4 *q2, i
     N.x = v[0].w; N.y = v[1].w; N.z = v[2].w;
 }
 
-// If triangle j completes triangle i to a parallelogram, returns the rotation r of i's vertices that puts the
-// shared edge on (first, third); otherwise -1.
-__device__ int match(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int i, int j) {
-    if (mati[i] != mati[j]) return -1;
+struct Quad { int rot; double b, a; };   // rot: index of A's vertex opposite the shared edge
+
+// Can triangle j complete triangle i to a convex planar quad?  (rot < 0: no)
+__device__ Quad match(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int i, int j) {
+    Quad no = {-1, 1.0, 0.0};
+    if (mati[i] != mati[j]) return no;
     float4 a[3], b[3];
     D3 Na, Nb;
     load_tri(q0, q1, q2, i, a, Na);
     load_tri(q0, q1, q2, j, b, Nb);
-    if (!(dotd(Na, Nb) > 1.0 - 1e-9)) return -1;                 // same plane orientation (unit normals)
+    const D3 cr = crossd(Na, Nb);
+    if (!(dotd(Na, Nb) > 0.0) || !(dotd(cr, cr) <= 1e-10)) return no;     // normals within 1e-5 rad
     for (int r = 0; r < 3; ++r) {
-        const float4 x = a[r], z = a[(r + 1) % 3], y = a[(r + 2) % 3];   // rotated A = (x, z, y): diagonal x–y
+        const float4 z = a[r], y = a[(r + 1) % 3], x = a[(r + 2) % 3];
         int shared = 0, other = -1;
         for (int k = 0; k < 3; ++k) {
             if (same(b[k], x) || same(b[k], y)) shared++; else other = k;
         }
-        if (shared != 2 || other < 0) continue;
-        const D3 want = sub(add(d3(x), d3(y)), d3(z));            // x + y - z
-        const D3 got = d3(b[other]);
-        const D3 diff = sub(got, want);
-        const D3 e = sub(d3(y), d3(x));
-        const double scale = sqrt(dotd(e, e)) + 1e-30;
-        if (sqrt(dotd(diff, diff)) > 1e-5 * scale) continue;     // not a parallelogram
-        if (fabs(dotd(sub(got, d3(x)), Na)) > 1e-5 * scale) continue;   // not coplanar
-        return r;
+        if (shared != 2 || other < 0 || same(b[other], z)) continue;
+        const D3 e1 = sub(d3(y), d3(z)), e2 = sub(d3(x), d3(z)), w = sub(d3(b[other]), d3(z));
+        const double den = dotd(Na, crossd(e1, e2));
+        if (den == 0.0) continue;
+        const double scale = sqrt(fmax(dotd(e1, e1), dotd(e2, e2))) + 1e-30;
+        if (fabs(dotd(w, Na)) > 1e-5 * scale) continue;                     // far corner off the plane
+        const double du = dotd(crossd(e2, Na), w) / den, dv = dotd(crossd(Na, e1), w) / den;
+        if (!(du > 1e-6 && dv > 1e-6 && du + dv > 1.0 + 1e-6)) continue;    // not strictly convex
+        Quad q = {r, (1.0 - du) / dv, (1.0 - dv) / du};
+        return q;
     }
-    return -1;
+    return no;
 }
 
-__device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i, int rot, int partner,
-                     float4 *p0, float4 *p1, float4 *p2, float *f, int *rep, int slot) {
+__device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i, Quad q,
+                     float4 *p0, float4 *p1, float4 *p2, float2 *ab, int *rep, int slot) {
     float4 a[3];
     D3 N;
     load_tri(q0, q1, q2, i, a, N);
+    const int rot = q.rot < 0 ? 0 : q.rot;
     const D3 r1 = d3(a[rot]), r2 = d3(a[(rot + 1) % 3]), r3 = d3(a[(rot + 2) % 3]);
     const D3 e1 = sub(r2, r1), e2 = sub(r3, r1);
     const double inv = 1.0 / dotd(N, crossd(e1, e2));
@@ -76,13 +80,13 @@ __device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i
     p0[slot] = make_float4((float)N.x, (float)N.y, (float)N.z, (float)r1.x);
     p1[slot] = make_float4((float)r1.y, (float)r1.z, (float)(mu.x * inv), (float)(mu.y * inv));
     p2[slot] = make_float4((float)(mu.z * inv), (float)(mv.x * inv), (float)(mv.y * inv), (float)(mv.z * inv));
+    ab[slot] = make_float2((float)q.b, (float)q.a);
     rep[slot] = i;
-    f[slot] = partner >= 0 ? 1.0f : 0.0f;
 }
 
 // one block; n <= PRIMS_MAX_TRIS.  Greedy in upload order: triangle i takes the first unpaired j > i that matches.
 __global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int n,
-                              float4 *p0, float4 *p1, float4 *p2, float *f, int *rep, int *n_prims) {
+                              float4 *p0, float4 *p1, float4 *p2, float2 *ab, int *rep, int *n_prims) {
     __shared__ unsigned char used[PRIMS_MAX_TRIS];
     for (int i = threadIdx.x; i < n; i += blockDim.x) used[i] = 0;
     __syncthreads();
@@ -90,15 +94,16 @@ __global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *
         int slot = 0;
         for (int i = 0; i < n; ++i) {
             if (used[i]) continue;
-            int partner = -1, rot = 0;
+            Quad q = {-1, 1.0, 0.0};
+            int partner = -1;
             for (int j = i + 1; j < n && partner < 0; ++j) {
                 if (used[j]) continue;
-                const int r = match(q0, q1, q2, mati, i, j);
-                if (r >= 0) { partner = j; rot = r; }
+                const Quad m = match(q0, q1, q2, mati, i, j);
+                if (m.rot >= 0) { partner = j; q = m; }
             }
             used[i] = 1;
             if (partner >= 0) used[partner] = 1;
-            emit(q0, q1, q2, i, rot, partner, p0, p1, p2, f, rep, slot++);
+            emit(q0, q1, q2, i, q, p0, p1, p2, ab, rep, slot++);
         }
         *n_prims = slot;
     }
@@ -107,6 +112,6 @@ __global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *
 }  // namespace
 
 void prims_build(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int n, float4 *p0, float4 *p1,
-                 float4 *p2, float *f, int *rep, int *n_prims_dev, cudaStream_t st) {
-    k_build_prims<<<1, 64, 0, st>>>(q0, q1, q2, mati, n, p0, p1, p2, f, rep, n_prims_dev);
+                 float4 *p2, float2 *ab, int *rep, int *n_prims_dev, cudaStream_t st) {
+    k_build_prims<<<1, 64, 0, st>>>(q0, q1, q2, mati, n, p0, p1, p2, ab, rep, n_prims_dev);
 }

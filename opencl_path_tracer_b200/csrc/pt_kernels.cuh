@@ -185,18 +185,17 @@ PT_DEV void brute_smem_pairs(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Clo
         closest_update(best, fminf(fminf(u.y, v.y), q.y) >= 0.0f, t.y, 2 * j + 1);
     }
 }
-// The same scan over merged primitives (prims.cu): a parallelogram (two coplanar triangles sharing their diagonal)
-// costs one triangle test plus two packed ops: inside iff min(v, 1-v, 1-(u+v), u + f*v) >= 0, f = 1 for a
-// parallelogram and 0 for a lone triangle.  best.tri receives the PRIMITIVE index.
+// The same scan over merged primitives (prims.cu): a convex planar quad (two coplanar triangles sharing a
+// diagonal) costs one triangle test: inside iff min(u, v, 1 - u - b*v, 1 - v - a*u) >= 0, with (b, a) = (1, 0)
+// for a lone triangle.  7 float4 per pair, the last holds (-b.x, -b.y, -a.x, -a.y).  best.tri = PRIMITIVE index.
 template <int U>
-PT_DEV void brute_smem_prims(const float4 *s_pairs, const float2 *s_f, int n_pairs, V3 P, V3 V, Closest &best) {
+PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Closest &best) {
     const RayPair r = ray_pair(P, V);
     const float2 one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
 #pragma unroll U
     for (int j = 0; j < n_pairs; ++j) {
-        const float4 L0 = s_pairs[6 * j], L1 = s_pairs[6 * j + 1], L2 = s_pairs[6 * j + 2];
-        const float4 L3 = s_pairs[6 * j + 3], L4 = s_pairs[6 * j + 4], L5 = s_pairs[6 * j + 5];
-        const float2 f = s_f[j];
+        const float4 L0 = s_pairs[7 * j], L1 = s_pairs[7 * j + 1], L2 = s_pairs[7 * j + 2];
+        const float4 L3 = s_pairs[7 * j + 3], L4 = s_pairs[7 * j + 4], L5 = s_pairs[7 * j + 5], L6 = s_pairs[7 * j + 6];
         const float2 Nx = make_float2(L0.x, L0.y), Ny = make_float2(L0.z, L0.w), Nz = make_float2(L1.x, L1.y);
         const float2 wx = __fadd2_rn(make_float2(L1.z, L1.w), r.Px);
         const float2 wy = __fadd2_rn(make_float2(L2.x, L2.y), r.Py);
@@ -207,11 +206,10 @@ PT_DEV void brute_smem_prims(const float4 *s_pairs, const float2 *s_f, int n_pai
         const float2 px = __ffma2_rn(r.Vx, t, wx), py = __ffma2_rn(r.Vy, t, wy), pz = __ffma2_rn(r.Vz, t, wz);
         const float2 u = dot2(make_float2(L3.x, L3.y), make_float2(L3.z, L3.w), make_float2(L4.x, L4.y), px, py, pz);
         const float2 v = dot2(make_float2(L4.z, L4.w), make_float2(L5.x, L5.y), make_float2(L5.z, L5.w), px, py, pz);
-        const float2 q = __ffma2_rn(__fadd2_rn(u, v), neg1, one);              // 1 - (u + v)
-        const float2 w = __ffma2_rn(v, neg1, one);                             // 1 - v
-        const float2 e = __ffma2_rn(f, v, u);                                  // u (triangle) or u + v (parallelogram)
-        closest_update(best, fminf(fminf(fminf(v.x, w.x), q.x), e.x) >= 0.0f, t.x, 2 * j);
-        closest_update(best, fminf(fminf(fminf(v.y, w.y), q.y), e.y) >= 0.0f, t.y, 2 * j + 1);
+        const float2 q = __ffma2_rn(v, make_float2(L6.x, L6.y), __ffma2_rn(u, neg1, one));     // 1 - u - b*v
+        const float2 w = __ffma2_rn(u, make_float2(L6.z, L6.w), __ffma2_rn(v, neg1, one));     // 1 - v - a*u
+        closest_update(best, fminf(fminf(u.x, v.x), fminf(q.x, w.x)) >= 0.0f, t.x, 2 * j);
+        closest_update(best, fminf(fminf(u.y, v.y), fminf(q.y, w.y)) >= 0.0f, t.y, 2 * j + 1);
     }
 }
 #endif
@@ -484,22 +482,21 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
         __syncthreads();
     }
     const int n_prim_pairs = (sc.n_prims + 1) >> 1;
-    const float2 *s_f = reinterpret_cast<const float2 *>(s_tris + 6 * n_prim_pairs);
-    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) {      // pair layout over the merged primitives + their f flags
-        float2 *sf = reinterpret_cast<float2 *>(s_tris + 6 * n_prim_pairs);
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) {      // pair layout over the merged primitives + their edge slopes
         for (int j = threadIdx.x; j < n_prim_pairs; j += PT_BLOCK) {
             const int ia = 2 * j, ib = 2 * j + 1;
             const bool hb = ib < sc.n_prims;
             const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);     // padding primitive: N = 0 -> t = NaN -> never accepted
             const float4 A0 = ldg4(sc.pq0 + ia), A1 = ldg4(sc.pq1 + ia), A2 = ldg4(sc.pq2 + ia);
             const float4 B0 = hb ? ldg4(sc.pq0 + ib) : z, B1 = hb ? ldg4(sc.pq1 + ib) : z, B2 = hb ? ldg4(sc.pq2 + ib) : z;
-            s_tris[6 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
-            s_tris[6 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
-            s_tris[6 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
-            s_tris[6 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
-            s_tris[6 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
-            s_tris[6 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
-            sf[j] = make_float2(__ldg(sc.prim_f + ia), hb ? __ldg(sc.prim_f + ib) : 0.0f);
+            const float2 sa = __ldg(sc.prim_ab + ia), sb = hb ? __ldg(sc.prim_ab + ib) : make_float2(1.0f, 0.0f);
+            s_tris[7 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
+            s_tris[7 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
+            s_tris[7 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
+            s_tris[7 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
+            s_tris[7 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
+            s_tris[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
+            s_tris[7 * j + 6] = make_float4(-sa.x, -sb.x, -sa.y, -sb.y);
         }
         __syncthreads();
     }
@@ -550,7 +547,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
 #if !PT_PARITY
             if (SMEM == 2) brute_smem_pairs<U>(s_tris, (sc.n_tris + 1) >> 1, rayP, rayD, best); else
             if (SMEM == 3) {
-                brute_smem_prims<U>(s_tris, s_f, n_prim_pairs, rayP, rayD, best);
+                brute_smem_prims<U>(s_tris, n_prim_pairs, rayP, rayD, best);
                 if (best.t < PT_NO_HIT) best.tri = __ldg(sc.prim_rep + best.tri);
             } else
 #endif
@@ -624,7 +621,7 @@ static void launch_one(const RenderParams &p, cudaStream_t st) {
     size_t smem = 0;
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 1) smem = (size_t)p.sc.n_tris * 3 * sizeof(float4);
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) smem = (size_t)((p.sc.n_tris + 1) / 2) * 6 * sizeof(float4);
-    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) smem = (size_t)((p.sc.n_prims + 1) / 2) * (6 * sizeof(float4) + sizeof(float2));
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) smem = (size_t)((p.sc.n_prims + 1) / 2) * 7 * sizeof(float4);
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM, MINB, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_render<ACCEL, COUNT, SMEM, MINB, U><<<grid, PT_BLOCK, smem, st>>>(p);
@@ -637,7 +634,7 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
         if (smem) {
             if (c) launch_one<PT_ACCEL_BRUTE, true, 1>(p, st);
 #if !PT_PARITY
-            else if (p.sc.n_prims > 0) launch_one<PT_ACCEL_BRUTE, false, 3, 8, 4>(p, st);   // same scan over merged parallelograms (prims.cu)
+            else if (p.sc.n_prims > 0) launch_one<PT_ACCEL_BRUTE, false, 3, 8, 4>(p, st);   // same scan over merged convex quads (prims.cu)
             else launch_one<PT_ACCEL_BRUTE, false, 2, 8, 4>(p, st);   // packed-FP32 pair scan; 64 registers -> 8 blocks/SM, 4 pairs in flight
                                                                       // (measured best of 8 (occupancy, unroll) variants: 23.0 vs 20.7 Grays/s)
 #else

@@ -36,7 +36,7 @@ struct SceneDev {
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
     // merged scan primitives for the fast brute-force scan (prims.cu); n_prims == 0: not built / nothing merged
     const float4 *pq0, *pq1, *pq2;// fast layout
-    const float *prim_f;          // 1: parallelogram of two triangles, 0: lone triangle
+    const float2 *prim_ab;        // edge slopes (b, a) of the quad's two far edges; (1, 0) for a lone triangle
     const int *prim_rep;          // primitive → upload index of the triangle that stands for it
     int n_prims;
 };

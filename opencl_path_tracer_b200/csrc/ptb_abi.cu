@@ -53,7 +53,7 @@ struct Staged {                        // device-internal copy of the scene, val
     int lbvh_leaf = 0;
     // merged scan primitives (prims.cu), built on first use by a fast brute-force launch
     float4 *p0 = nullptr, *p1 = nullptr, *p2 = nullptr;
-    float *prim_f = nullptr;
+    float2 *prim_ab = nullptr;
     int *prim_rep = nullptr, *n_prims_dev = nullptr;
     int n_prims = 0;
     bool prims_valid = false;
@@ -186,7 +186,7 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
     return PTB_SUCCESS;
 }
 
-// Merge coplanar same-material triangle pairs into parallelograms for the fast shared-memory scan (prims.cu).
+// Merge coplanar same-material triangle pairs into convex quads for the fast shared-memory scan (prims.cu).
 // Leaves n_prims = 0 when nothing merges, so the launch keeps the plain triangle scan.
 int ensure_prims() {
     Staged &s = G.staged;
@@ -198,11 +198,11 @@ int ensure_prims() {
         CUDA_OK(cudaMalloc((void **)&s.p0, PRIMS_MAX_TRIS * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.p1, PRIMS_MAX_TRIS * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.p2, PRIMS_MAX_TRIS * sizeof(float4)));
-        CUDA_OK(cudaMalloc((void **)&s.prim_f, PRIMS_MAX_TRIS * sizeof(float)));
+        CUDA_OK(cudaMalloc((void **)&s.prim_ab, PRIMS_MAX_TRIS * sizeof(float2)));
         CUDA_OK(cudaMalloc((void **)&s.prim_rep, PRIMS_MAX_TRIS * sizeof(int)));
         CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
     }
-    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_f, s.prim_rep, s.n_prims_dev, G.stream);
+    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.n_prims_dev, G.stream);
     CUDA_OK(cudaGetLastError());
     G.launches++;
     int n = 0;
@@ -271,7 +271,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
         rc = ensure_prims();
         if (rc) return rc;
-        p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_f = s.prim_f; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
+        p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_ab = s.prim_ab; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
     }
     p.sc.mats = (const RefMaterial *)mats->dptr;
     p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
@@ -398,7 +398,7 @@ int ptb_shutdown(void) {
     G.mems.clear();
     Staged &s = G.staged;
     cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
-    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_f); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
+    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
     lbvh_free(&s.lbvh);
     s = Staged();
     cudaFree(G.counters);

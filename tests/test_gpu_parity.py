@@ -65,7 +65,7 @@ def test_fast_math_within_tolerance(ptb, cornell_ref, accel):
     assert st["rmse_over_mean"] <= 0.01, st
 
 
-def test_merged_parallelograms_match_triangle_scan(ptb, cornell_ref):
+def test_merged_quads_match_triangle_scan(ptb, cornell_ref):
     """Fast brute-force scan over merged primitives (prims.cu) vs. the same scan over the plain triangles:
     the Cornell box's fan-triangulated quads must merge, and the image must stay within the fast tolerance."""
     try:
