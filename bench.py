@@ -321,6 +321,8 @@ def main():
                 "traffic": None, "kernel": "k_render (fused gen_ray + trace_ray + accumulate)",
                 "peak_source": f"{sms} SMs x 128 FP32 lanes x 2 x {sm_max:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); the path has no dense contraction "
                                "and ~0 mandatory HBM traffic, so neither the hbm nor the tensor roofline bounds it (SURVEY 8d)",
+                "numerator": "algorithmic flops of the reference's closest-hit search for this scene (counting pass over the plain triangles); "
+                             "the shipping scan may execute fewer (merged quad primitives, config.scan_primitives)",
                 "flops_per_ray": f_ray, "box_tests_per_ray": B, "tri_tests_per_ray": T,
                 "tri_stage_fractions": [T1 / max(T, 1e-9), T2 / max(T, 1e-9), T3 / max(T, 1e-9)],
                 "hbm_secondary": {"algorithmic_bytes_per_step": W * H * (4 + 4 + 16 + 16), "note": "seed read + state/colors/image write per pixel per launch"}}
@@ -345,6 +347,7 @@ def main():
             "data": "synthetic", "spp_per_s": spp * world * args.steps / (total_ms * 1e-3),
             "rays_per_step": total_rays / args.steps,
             "config": {"workload": args.workload, "width": W, "height": H, "spp_per_gpu_per_step": spp, "depth": depth, "triangles": n_tris,
+                       "scan_primitives": int(ptb.scan_prims()) if accel_used.startswith("brute") and args.math == "fast" else None,
                        "accel": accel_used, "math": args.math, "pipeline": args.pipeline,
                        "parallelism": "single GPU" if world == 1 else f"spp-split x{world} + NCCL reduce(SUM) of the accumulation buffer per step",
                        "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s},

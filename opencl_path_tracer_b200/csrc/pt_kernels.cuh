@@ -64,6 +64,19 @@ PT_DEV void camera_get_ray_xy(int px, int py, const RefCamera &cam, float rnd1, 
     P = eye;
     D = normalize(p - eye);
 }
+// Launch-level form: the parity flavour evaluates prog.cl's expressions literally; the fast flavour uses the
+// folded affine map of pt_params.h (6 FMAs + normalize instead of two divisions and the basis arithmetic)
+PT_DEV void camera_ray(const RenderParams &p, int px, int py, float rnd1, float rnd2, V3 &P, V3 &D) {
+#if PT_PARITY
+    camera_get_ray_xy(px, py, p.cam, rnd1, rnd2, P, D);
+#else
+    const float x = (float)px + rnd1, y = (float)py + rnd2;
+    P = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
+    D = normalize(v3(fmaf(p.cam_dy.x, y, fmaf(p.cam_dx.x, x, p.cam_o.x)),
+                     fmaf(p.cam_dy.y, y, fmaf(p.cam_dx.y, x, p.cam_o.y)),
+                     fmaf(p.cam_dy.z, y, fmaf(p.cam_dx.z, x, p.cam_o.z))));
+#endif
+}
 PT_DEV void camera_get_ray(int id, const RefCamera &cam, float rnd1, float rnd2, V3 &P, V3 &D) {
     int X = (int)cam.XM;
     camera_get_ray_xy(id % X, id / X, cam, rnd1, rnd2, P, D);
@@ -433,8 +446,13 @@ PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32
         } else {
             new_ray_specular(hitP, N, oldD, rayP, rayD);
         }
+#if PT_PARITY
         if (before != ps.in) ps.fR = (ps.fR * (1.0f - F)) * (1.0f / (1.0f - prob));
         else ps.fR = (ps.fR * F) * (1.0f / prob);
+#else   // fS and fR only ever appear as the product fS*fR (prog.cl:363): the fast flavour keeps one factor, fR stays 1
+        if (before != ps.in) ps.fS = (ps.fS * (1.0f - F)) * (1.0f / (1.0f - prob));
+        else ps.fS = (ps.fS * F) * (1.0f / prob);
+#endif
     }
     // any other type: ray unchanged, nothing added
 }
@@ -534,7 +552,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
                 rayP = v3(r[0]); rayD = v3(r[1]);
             } else {                                             // gen_ray fused, prog.cl:384-389
                 float r1 = pt_rand(rng), r2 = pt_rand(rng);
-                camera_get_ray_xy(cam_x, cam_y, p.cam, r1, r2, rayP, rayD);
+                camera_ray(p, cam_x, cam_y, r1, r2, rayP, rayD);
             }
             path_reset(ps);
             depth = 0;
@@ -543,6 +561,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
         if (!__any_sync(0xffffffffu, alive)) break;
         const bool trace = alive && depth < p.iterations;        // iterations <= 0: the bounce loop body never runs
         Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+        const Work wk_before = wk;
         if (ACCEL == PT_ACCEL_BRUTE) {                           // converged scan: idle lanes scan too (free)
 #if !PT_PARITY
             if (SMEM == 2) brute_smem_pairs<U>(s_tris, (sc.n_tris + 1) >> 1, rayP, rayD, best); else
@@ -553,6 +572,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
 #endif
             if (SMEM == 1) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
             else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
+            if (COUNT && !trace) wk = wk_before;                 // ... but only real rays count as work
         } else if (trace) {
             if (ACCEL == PT_ACCEL_REFBVH) refbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
             else lbvh_intersect<COUNT>(sc, rayP, rayD, best, wk);
@@ -607,7 +627,8 @@ __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n)
     uint32_t rng = (uint32_t)p.rnds[id];
     float r1 = pt_rand(rng), r2 = pt_rand(rng);
     V3 P, D;
-    camera_get_ray((int)id, p.cam, r1, r2, P, D);
+    const int camX = max((int)p.cam.XM, 1);
+    camera_ray(p, (int)id % camX, (int)id / camX, r1, r2, P, D);
     p.rnds[id] = (int)rng;
     float4 *r = reinterpret_cast<float4 *>(p.rays + id);
     r[0] = make_float4(P.x, P.y, P.z, 0.0f);

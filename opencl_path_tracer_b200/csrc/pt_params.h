@@ -44,6 +44,9 @@ struct SceneDev {
 struct RenderParams {
     SceneDev sc;
     RefCamera cam;                // trace_ray arg 11 / gen_ray arg 1
+    // the same camera as one affine map of the jittered pixel position (fast flavour only, set by pt_cam_affine):
+    // p - eye = cam_o + cam_dx * (px + rnd1) + cam_dy * (py + rnd2)   (prog.cl:82-92 with the constants folded)
+    float4 cam_o, cam_dx, cam_dy;
     int *rnds;                    // per-pixel RNG state (main.cpp:509,522-526)
     float4 *colors;               // float3[W*H], 16 B each (main.cpp:520)
     float4 *tex;                  // RGBA float image or nullptr (main.cpp:512-519)
@@ -64,6 +67,22 @@ struct RenderParams {
     int *wf_queue[2];             // active pixel ids, double buffered
     int *wf_ctrl;                 // [0],[1] queue lengths, [2] fetch cursor of the trace kernel, [3] spare
 };
+
+static inline void pt_cam_affine(RenderParams &p) {
+    const RefCamera &c = p.cam;
+    const double X = (double)(int)c.XM, Y = (double)(int)c.YM;
+    const double e[3] = {c.eye.x, c.eye.y, c.eye.z}, l[3] = {c.lookat.x, c.lookat.y, c.lookat.z};
+    const double u[3] = {c.up.x, c.up.y, c.up.z}, r[3] = {c.right.x, c.right.y, c.right.z};
+    float o[3], dx[3], dy[3];
+    for (int k = 0; k < 3; ++k) {
+        o[k] = (float)(l[k] - e[k] - r[k] - u[k]);
+        dx[k] = (float)(X > 0 ? 2.0 * r[k] / X : 0.0);
+        dy[k] = (float)(Y > 0 ? 2.0 * u[k] / Y : 0.0);
+    }
+    p.cam_o = make_float4(o[0], o[1], o[2], 0.0f);
+    p.cam_dx = make_float4(dx[0], dx[1], dx[2], 0.0f);
+    p.cam_dy = make_float4(dy[0], dy[1], dy[2], 0.0f);
+}
 
 // one entry per translation unit; implemented in pt_kernels.cuh
 namespace pt_parity {

@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render_sched(const RenderPar
                         rayP = v3(r[0]); rayD = v3(r[1]);
                     } else {
                         float r1 = pt_rand(rng), r2 = pt_rand(rng);
-                        camera_get_ray_xy(cam_x, cam_y, p.cam, r1, r2, rayP, rayD);
+                        camera_ray(p, cam_x, cam_y, r1, r2, rayP, rayD);
                     }
                     path_reset(ps);
                     depth = 0;

@@ -60,7 +60,7 @@ PT_DEV bool wf_next_sample(const RenderParams &p, int i, WfPath &w, V3 &rayP, V3
     const int camX = (int)p.cam.XM;
     while (w.s < s_end) {
         float r1 = pt_rand(w.rng), r2 = pt_rand(w.rng);
-        camera_get_ray_xy(i % max(camX, 1), i / max(camX, 1), p.cam, r1, r2, rayP, rayD);
+        camera_ray(p, i % max(camX, 1), i / max(camX, 1), r1, r2, rayP, rayD);
         path_reset(w.ps);
         w.depth = 0;
         if (p.iterations > 0) return true;

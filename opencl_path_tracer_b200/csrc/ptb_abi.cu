@@ -299,6 +299,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.sum_mode = G.sum_mode;
     p.count_work = G.count_work;
     p.counters = G.counters;
+    pt_cam_affine(p);
     return PTB_SUCCESS;
 }
 
@@ -309,6 +310,7 @@ int run_gen_ray(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n) 
     RenderParams p;
     memset(&p, 0, sizeof p);
     p.cam = cam;
+    pt_cam_affine(p);
     p.rays = (RefRay *)rays->dptr;
     p.rnds = (int *)rnds->dptr;
     p.shard_rank = G.shard_rank; p.shard_n = G.shard_n; p.shard_group = G.shard_group;

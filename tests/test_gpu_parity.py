@@ -96,13 +96,16 @@ def test_depth1_preview_is_exact(ptb):
     assert (rnds == ref["rnds"]).all()
 
 
-def test_work_counters_match_reference(ptb):
-    """rays / box tests / triangle tests of the REFBVH traversal equal the reference's own counts."""
+@pytest.mark.parametrize("accel", [capi.ACCEL_REFBVH, capi.ACCEL_BRUTE])
+def test_work_counters_match_reference(ptb, accel):
+    """rays / box tests / triangle tests of the REFBVH traversal and of the brute-force scan (prog.cl:318)
+    equal the reference's own counts (idle lanes of the converged scan are not work)."""
     if not util.have_ref_cpu():
         pytest.skip("oracle/_ref/ref_cpu not built")
-    ref = util.run_ref_cpu(96, 64, 2, 4, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3, count=True)
+    ref = util.run_ref_cpu(96, 64, 2, 4, obj=util.CORNELL, eye=(277.5, 277.5, -800), fov=39.3,
+                           count=accel != capi.ACCEL_BRUTE, brute=accel == capi.ACCEL_BRUTE)
     surf = host.load_ptbd(ref["files"]["dump"])
-    ptb.set_accel(capi.ACCEL_REFBVH)
+    ptb.set_accel(accel)
     ptb.set_math(capi.MATH_PARITY)
     ptb.set_count_work(1)
     ptb.reset_counters()
@@ -110,6 +113,10 @@ def test_work_counters_match_reference(ptb):
     s.render_spp(2)
     c = ptb.counters()
     ptb.set_count_work(0)
+    if accel == capi.ACCEL_BRUTE:     # the reference's brute-force build carries no counters: every ray tests every triangle
+        assert c["rays"] == ref["info"]["rays"], (c, ref["info"])
+        assert c["tri_tests"] == ref["info"]["tris"] * c["rays"] and c["box_tests"] == 0, c
+        return
     for k in ("rays", "box_tests", "tri_tests", "tri_stage1", "tri_stage2", "tri_stage3"):
         assert c[k] == ref["info"][k], (k, c, ref["info"])
 
