@@ -68,6 +68,15 @@ int ptb_release(ptb_mem m);
 int ptb_write(ptb_mem m, size_t offset, size_t bytes, const void *src);   /* blocking */
 int ptb_read(ptb_mem m, size_t offset, size_t bytes, void *dst);          /* blocking; the reference's read-back is dead code (main.cpp:690,728) */
 size_t ptb_mem_size(ptb_mem m);
+/* Scene ingest on the device — replaces the vertex loop of Scene::add_Obj (main.cpp:589-612: negate x, rotate_x(pitch),
+ * rotate_y(yaw), *scale+pos) and the Triangle constructor (main.cpp:144-166: unit normal) for one triangulated mesh:
+ * vertices = attrib.vertices (3 floats each), indices = 3 vertex indices per face, mat_ids = material per face, all HOST
+ * pointers as tiny_obj_loader leaves them.  Writes n_faces 80-byte Triangle records into `tris` starting at record
+ * first_tri, bit-identical to what the reference host computes.  The records stay in face order (no host tree is
+ * built for them: pass kd_tree_shift_size = 0 or keep the host trees for other objects only). Blocking. */
+int ptb_ingest_mesh(ptb_mem tris, size_t first_tri, const float *vertices, size_t n_verts, const int *indices,
+                    const int *mat_ids, size_t n_faces, const float *pos, const float *scale, float pitch_deg,
+                    float yaw_deg, int mat_offset);
 /* extensions for hosts that own device memory already (torch tensors, NCCL buffers) */
 ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes);  /* non-owning handle */
 void *ptb_device_ptr(ptb_mem m);

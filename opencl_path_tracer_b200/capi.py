@@ -15,7 +15,7 @@ PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO = 0, 1, 2
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py against the header text)
 SYMBOLS = [
     "ptb_init", "ptb_shutdown", "ptb_device_string", "ptb_device_compute_units", "ptb_backend_name",
-    "ptb_alloc", "ptb_alloc_image", "ptb_retain", "ptb_release", "ptb_write", "ptb_read", "ptb_mem_size",
+    "ptb_alloc", "ptb_alloc_image", "ptb_retain", "ptb_release", "ptb_write", "ptb_read", "ptb_mem_size", "ptb_ingest_mesh",
     "ptb_wrap_device", "ptb_device_ptr", "ptb_kernel_id", "ptb_set_arg", "ptb_set_arg_mem", "ptb_launch",
     "ptb_finish", "ptb_last_error", "ptb_clear_error", "ptb_set_accel", "ptb_set_math", "ptb_set_pipeline",
     "ptb_set_fuse_gen", "ptb_set_lbvh_leaf", "ptb_set_merge_prims", "ptb_scan_prims", "ptb_get_accel", "ptb_build_accel", "ptb_render",
@@ -54,6 +54,7 @@ def load_library(path=None):
         "ptb_device_compute_units": (i, []), "ptb_backend_name": (cp, []),
         "ptb_alloc": (u64, [sz]), "ptb_alloc_image": (u64, [i, i]), "ptb_retain": (i, [u64]), "ptb_release": (i, [u64]),
         "ptb_write": (i, [u64, sz, sz, vp]), "ptb_read": (i, [u64, sz, sz, vp]), "ptb_mem_size": (sz, [u64]),
+        "ptb_ingest_mesh": (i, [u64, sz, vp, sz, vp, vp, sz, vp, vp, C.c_float, C.c_float, i]),
         "ptb_wrap_device": (u64, [vp, sz]), "ptb_device_ptr": (vp, [u64]),
         "ptb_kernel_id": (i, [cp]), "ptb_set_arg": (i, [i, i, sz, vp]), "ptb_set_arg_mem": (i, [i, i, u64]),
         "ptb_launch": (i, [i, sz, sz]), "ptb_finish": (i, []), "ptb_last_error": (cp, []), "ptb_clear_error": (None, []),
@@ -88,6 +89,9 @@ class Ptb:
 
     def last_error(self):
         return self.lib.ptb_last_error().decode()
+
+    def clear_error(self):
+        self.lib.ptb_clear_error()
 
     def backend_name(self):
         return self.lib.ptb_backend_name().decode()
@@ -130,6 +134,19 @@ class Ptb:
 
     def read_ptr(self, h, ptr, nbytes, offset=0):
         self._ck(self.lib.ptb_read(h, offset, nbytes, ptr), "ptb_read")
+
+    def ingest_mesh(self, h, first_tri, vertices, faces, mat_ids, pos, scale, pitch, yaw, mat_offset):
+        """ptb_ingest_mesh: transform + normals + Triangle records on the device (main.cpp:589-612, 144-166)."""
+        v = np.ascontiguousarray(vertices, dtype=np.float32).reshape(-1, 3)
+        f = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+        m = np.ascontiguousarray(mat_ids, dtype=np.int32).reshape(-1)
+        if len(m) != len(f):
+            raise ValueError("one material id per face")
+        ps = np.ascontiguousarray(pos, dtype=np.float32).reshape(3)
+        sc = np.ascontiguousarray(scale, dtype=np.float32).reshape(3)
+        self._ck(self.lib.ptb_ingest_mesh(h, first_tri, v.ctypes.data, len(v), f.ctypes.data, m.ctypes.data, len(f),
+                                          ps.ctypes.data, sc.ctypes.data, float(pitch), float(yaw), int(mat_offset)),
+                 "ptb_ingest_mesh")
 
     def upload(self, array):
         a = np.ascontiguousarray(array)

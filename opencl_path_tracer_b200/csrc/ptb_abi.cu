@@ -7,6 +7,7 @@
 // and enqueues the fused path kernel on one in-order stream.  There is no CPU path: every entry
 // point that needs the device fails loudly when CUDA is not available.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -16,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "ingest.h"
 #include "lbvh.h"
 #include "prims.h"
 #include "pt_params.h"
@@ -498,6 +500,48 @@ int ptb_read(ptb_mem h, size_t off, size_t bytes, void *dst) {
     if (rc) return rc;
     CUDA_OK(cudaMemcpyAsync(dst, (const char *)m->dptr + off, bytes, cudaMemcpyDeviceToHost, G.stream));
     CUDA_OK(cudaStreamSynchronize(G.stream));
+    return PTB_SUCCESS;
+}
+int ptb_ingest_mesh(ptb_mem tris_h, size_t first_tri, const float *vertices, size_t n_verts, const int *indices,
+                    const int *mat_ids, size_t n_faces, const float *pos, const float *scale, float pitch_deg,
+                    float yaw_deg, int mat_offset) {
+    NEED_INIT();
+    MemObj *m = find(tris_h);
+    if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_ingest_mesh: bad handle");
+    if (n_faces == 0) return PTB_SUCCESS;
+    if (!vertices || !indices || !mat_ids || !pos || !scale) return fail(PTB_ERR_INVALID_VALUE, "ptb_ingest_mesh: null argument");
+    if ((first_tri + n_faces) * sizeof(RefTriangle) > m->bytes)
+        return fail(PTB_ERR_INVALID_VALUE, "ptb_ingest_mesh: triangles [%zu,%zu) outside a %zu-byte buffer", first_tri, first_tri + n_faces, m->bytes);
+    for (size_t i = 0; i < 3 * n_faces; ++i)
+        if (indices[i] < 0 || (size_t)indices[i] >= n_verts)
+            return fail(PTB_ERR_INVALID_VALUE, "ptb_ingest_mesh: vertex index %d of face %zu outside [0,%zu)", indices[i], i / 3, n_verts);
+    int rc = flush_pending();
+    if (rc) return rc;
+    IngestXform x;
+    // main.cpp:56,64: the angle is narrowed to float before cos/sin (double functions of <math.h>)
+    const float pitch = pitch_deg / 180.0f * 3.141593f, yaw = yaw_deg / 180.0f * 3.141593f;
+    x.cos_pitch = cos((double)pitch); x.sin_pitch = sin((double)pitch);
+    x.cos_yaw = cos((double)yaw); x.sin_yaw = sin((double)yaw);
+    for (int k = 0; k < 3; ++k) { x.scale[k] = scale[k]; x.pos[k] = pos[k]; }
+    x.mat_offset = mat_offset;
+    float *dv = nullptr;
+    int *di = nullptr, *dm = nullptr;
+    const size_t vb = n_verts * 3 * sizeof(float), ib = n_faces * 3 * sizeof(int), mb = n_faces * sizeof(int);
+    cudaError_t e = cudaMalloc((void **)&dv, vb);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&di, ib);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&dm, mb);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, vertices, vb, cudaMemcpyHostToDevice, G.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(di, indices, ib, cudaMemcpyHostToDevice, G.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dm, mat_ids, mb, cudaMemcpyHostToDevice, G.stream);
+    if (e == cudaSuccess) {
+        ingest_launch(dv, di, dm, n_faces, x, (RefTriangle *)m->dptr + first_tri, G.stream);
+        e = cudaGetLastError();
+        G.launches++;
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    cudaFree(dv); cudaFree(di); cudaFree(dm);
+    if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_ingest_mesh: %s", cudaGetErrorString(e));
+    m->version++;
     return PTB_SUCCESS;
 }
 size_t ptb_mem_size(ptb_mem h) {

@@ -276,6 +276,7 @@ class Scene:
         self.ptb = ptb or capi.Ptb(device)
         self.tris = np.zeros(0, dtype=TRIANGLE)
         self._pending = []
+        self._device_meshes = []
         self.tri_shift = 0
         self.kd_tree = []
         self.kd_tree_shift = []
@@ -336,10 +337,27 @@ class Scene:
             self.add_Triangle(Triangles(v[f[:, 0]], v[f[:, 1]], v[f[:, 2]], mat_offset + np.asarray(s["mats"])))
             self.end_Obj()
 
+    def add_Obj_device(self, file, pos, scale, pitch, yaw):
+        """add_Obj with the vertex transform, the normals and the Triangle records computed ON THE DEVICE
+        (ptb_ingest_mesh) at upload_Triangles(): only the OBJ/MTL text parse stays on the host.  The records are
+        bit-identical to add_Obj's, in face order; no reference tree is built for them (the LBVH takes them)."""
+        verts, shapes, mtl = load_obj(file)
+        mat_offset = len(self.mats)
+        for m in mtl:
+            self.add_Material(Material(m["Kd"], m["Ks"], m["Ke"], m["Kn"], m["Kk"], m["Ns"], m["Tp"]))
+        for s in shapes:
+            self.add_Mesh_device(verts, s["faces"], s["mats"], pos, scale, pitch, yaw, mat_offset)
+
+    def add_Mesh_device(self, verts, faces, mat_ids, pos=(0, 0, 0), scale=(1, 1, 1), pitch=0.0, yaw=0.0, mat_offset=0):
+        self._device_meshes.append((np.asarray(verts, dtype=np.float32), np.asarray(faces, dtype=np.int32),
+                                    np.asarray(mat_ids, dtype=np.int32), pos, scale, pitch, yaw, mat_offset))
+
     # main.cpp:618-630
     def upload_Triangles(self):
         self._flush()
         p = self.ptb
+        if self._device_meshes:
+            return self._upload_with_device_ingest()
         for h in (self.buffer_kd_tree, self.buffer_kd_tree_shift, self.buffer_tris):
             if h:
                 p.release(h)
@@ -349,6 +367,26 @@ class Scene:
         self.buffer_kd_tree_shift = p.upload(np.asarray(self.kd_tree_shift, dtype=np.int32))
         self.tris_size = len(self.tris)
         self.buffer_tris = p.upload(self.tris)
+
+    def _upload_with_device_ingest(self):
+        """host-built records first (their reference trees are dropped: indices into a longer array would still be
+        valid, but a scene that mixes both is traversed by the LBVH as one), then every device mesh in call order"""
+        p = self.ptb
+        for h in (self.buffer_kd_tree, self.buffer_kd_tree_shift, self.buffer_tris):
+            if h:
+                p.release(h)
+        n_dev = sum(len(m[1]) for m in self._device_meshes)
+        self.tris_size = len(self.tris) + n_dev
+        self.buffer_tris = p.alloc(max(self.tris_size, 1) * TRIANGLE.itemsize)
+        if len(self.tris):
+            p.write(self.buffer_tris, self.tris)
+        first = len(self.tris)
+        for verts, faces, mats, pos, scale, pitch, yaw, mat_offset in self._device_meshes:
+            p.ingest_mesh(self.buffer_tris, first, verts, faces, mats, pos, scale, pitch, yaw, mat_offset)
+            first += len(faces)
+        self.buffer_kd_tree = p.upload(np.zeros(1, dtype=NODE))
+        self.kd_tree_shift_size = 0
+        self.buffer_kd_tree_shift = p.upload(np.zeros(1, dtype=np.int32))
 
     # main.cpp:631-634
     def upload_Materials(self):

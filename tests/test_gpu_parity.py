@@ -198,3 +198,88 @@ def test_wavefront_parity(ptb, mixed_ref, spheres_ref, which):
     st = util.compare(colors, ref["colors"])
     assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
     assert (rnds == ref["rnds"]).mean() >= 1.0 - 1e-4
+
+
+# ---------------------------------------------------------------- scene ingest on the device
+def _records_equal(a, b):
+    """bit patterns equal; a NaN (degenerate face: 0/0 normal) matches any NaN"""
+    for k in ("r1", "r2", "r3", "N"):
+        x, y = a[k][:, :3], b[k][:, :3]
+        same = (x.view(np.uint32) == y.view(np.uint32)) | (np.isnan(x) & np.isnan(y))
+        if not same.all():
+            bad = np.argwhere(~same)
+            print(k, len(bad), "mismatches; first:", bad[0], x[bad[0][0]], y[bad[0][0]])
+            return False
+    return np.array_equal(a["mati"], b["mati"])
+
+
+@pytest.mark.parametrize("pose", [((555, 0, 0), (1, 1, 1), 0.0, 0.0), ((12.5, -3.0, 40.0), (0.5, 2.0, 1.25), 33.0, -71.5)])
+def test_device_ingest_matches_host_records(ptb, pose):
+    """ptb_ingest_mesh writes the same 80-byte Triangle records (vertices and unit normal, bit for bit) as the host
+    mirror of Scene::add_Obj + the Triangle constructor (main.cpp:589-612, 144-166), itself checked against the
+    reference host's dumps in tests/test_host.py."""
+    pos, scale, pitch, yaw = pose
+    ref = host.Scene(ptb)
+    ref.build_trees = False
+    ref.add_Obj(util.CORNELL, pos, scale, pitch, yaw)
+    ref._flush()
+    dev = host.Scene(ptb)
+    dev.add_Obj_device(util.CORNELL, pos, scale, pitch, yaw)
+    dev.upload_Triangles()
+    got = ptb.read(dev.buffer_tris, host.TRIANGLE, dev.tris_size)
+    assert dev.tris_size == len(ref.tris) == 32
+    assert _records_equal(got, ref.tris)
+    assert len(dev.mats) == len(ref.mats)
+
+
+def test_device_ingest_large_random_mesh(ptb):
+    rng = np.random.default_rng(7)
+    verts = (rng.random((5000, 3), dtype=np.float32) - 0.5) * 800.0
+    faces = rng.integers(0, len(verts), size=(20000, 3), dtype=np.int32)
+    mats = rng.integers(0, 9, size=len(faces), dtype=np.int32)
+    pos, scale, pitch, yaw = (100.0, 50.0, -25.0), (1.5, 0.75, 1.0), -12.0, 205.0
+    v = verts.copy()
+    v[:, 0] = -v[:, 0]
+    v = host.rotate_y(host.rotate_x(v, pitch), yaw)
+    v = v * np.asarray(scale, dtype=np.float32) + np.asarray(pos, dtype=np.float32)
+    want = host.Triangles(v[faces[:, 0]], v[faces[:, 1]], v[faces[:, 2]], 3 + mats)
+    h = ptb.alloc(len(faces) * host.TRIANGLE.itemsize)
+    ptb.ingest_mesh(h, 0, verts, faces, mats, pos, scale, pitch, yaw, 3)
+    got = ptb.read(h, host.TRIANGLE, len(faces))
+    ptb.release(h)
+    # degenerate faces (repeated vertex) give NaN normals on both sides: compare bit patterns
+    assert _records_equal(got, want)
+    with pytest.raises(capi.PtbError):
+        ptb.ingest_mesh(h, 0, verts, faces, mats, pos, scale, pitch, yaw, 3)      # released handle
+    ptb.clear_error()                                                             # errors are sticky (SURVEY §8b)
+    h2 = ptb.alloc(10 * host.TRIANGLE.itemsize)
+    with pytest.raises(capi.PtbError):
+        ptb.ingest_mesh(h2, 0, verts, faces, mats, pos, scale, pitch, yaw, 3)     # buffer too small
+    ptb.clear_error()
+    bad = faces.copy(); bad[5, 1] = len(verts)
+    h3 = ptb.alloc(len(faces) * host.TRIANGLE.itemsize)
+    with pytest.raises(capi.PtbError):
+        ptb.ingest_mesh(h3, 0, verts, bad, mats, pos, scale, pitch, yaw, 3)       # index out of range
+    ptb.clear_error()
+    ptb.release(h2); ptb.release(h3)
+
+
+def test_device_ingested_scene_renders_like_host_scene(ptb, cornell_ref):
+    """Cornell ingested on the device (face order, LBVH / brute force) renders the reference image: closest hits do not
+    depend on the triangle order except through exact-t ties, which the Cornell box does not produce at this size."""
+    surf = host.load_ptbd(cornell_ref["files"]["dump"])
+    ptb.set_accel(capi.ACCEL_AUTO)
+    ptb.set_math(capi.MATH_PARITY)
+    ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    s = host.Scene(ptb)
+    s.init_Scene(W, H)
+    s.add_Obj_device(util.CORNELL, (555, 0, 0), (1, 1, 1), 0.0, 0.0)
+    s.upload_Triangles()
+    s.upload_Materials()
+    s.iterations = DEPTH
+    cam = np.array(surf["camera"])
+    s._camera = lambda: cam
+    s.render_spp(SPP)
+    ptb.finish()
+    st = util.compare(s.download_colors(), cornell_ref["colors"])
+    assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
