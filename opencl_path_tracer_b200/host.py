@@ -117,8 +117,10 @@ def Triangle(r1, r2, r3, mati):
     return Triangles([r1], [r2], [r3], [mati])[0]
 
 
-def Camera(width, height, fov, yaw, pitch, shift):
-    """main.cpp:311-347 with the interactive globals passed in (global_forward/rightward/upward = 0)."""
+def camera_step(width, height, fov, yaw, pitch, shift, move=(0.0, 0.0, 0.0)):
+    """main.cpp:311-347 — the Camera constructor INCLUDING its side effect: it integrates the interactive motion
+    (global_forward, global_rightward, global_upward) into global_shift along the rotated unit basis before the basis
+    is scaled.  Returns (Camera record, new global_shift).  All arithmetic in float, cos/sin/tan in double."""
     c = np.zeros((), dtype=CAMERA)
     XM, YM = f32(width), f32(height)
     up_len, right_len = f32(YM / f32(2.0)), f32(XM / f32(2.0))
@@ -126,12 +128,20 @@ def Camera(width, height, fov, yaw, pitch, shift):
     ahead_len = f32(np.float64(right_len) / np.tan(np.float64(ang)))
     basis = np.array([[0, 1, 0], [1, 0, 0], [0, 0, 1]], dtype=np.float32)    # up, right, ahead
     basis = rotate_y(rotate_x(basis, pitch), yaw)
+    fwd, rgt, upw = (f32(m) for m in move)
+    shift = np.asarray(shift, dtype=np.float32).copy()
+    # global_shift[i] = global_shift[i] + ahead[i]*forward + right[i]*rightward + up[i]*upward  (left to right, float)
+    shift = ((shift + basis[2] * fwd) + basis[1] * rgt) + basis[0] * upw
     up, right, ahead = basis[0] * up_len, basis[1] * right_len, basis[2] * ahead_len
-    shift = np.asarray(shift, dtype=np.float32)
     eye = np.array([f32(500.0) + shift[0], f32(500.0) + shift[1], f32(-1299.037842) + shift[2]], dtype=np.float32)
     c["eye"][:3], c["up"][:3], c["right"][:3], c["lookat"][:3] = eye, up, right, eye + ahead
     c["XM"], c["YM"] = XM, YM
-    return c
+    return c, shift.astype(np.float32)
+
+
+def Camera(width, height, fov, yaw, pitch, shift):
+    """main.cpp:311-347 with the interactive globals at rest (global_forward/rightward/upward = 0)."""
+    return camera_step(width, height, fov, yaw, pitch, shift)[0]
 
 
 def camera_at(width, height, fov, yaw, pitch, eye):
@@ -285,6 +295,7 @@ class Scene:
         self.current_sample = 0             # main.cpp:28
         self.global_fov, self.global_yaw, self.global_pitch = 75.0, -13.800002 - 50, 5.599997 + 10     # main.cpp:30-32
         self.global_shift = np.array([265.055481, 162.305969, 360.414001], dtype=np.float32)            # main.cpp:39
+        self.global_forward = self.global_rightward = self.global_upward = 0.0                          # main.cpp:33-35
         self.build_trees = True             # False: skip the host trees (they are optional for the CUDA path)
         self.buffer_tris = self.buffer_mats = self.buffer_kd_tree = self.buffer_kd_tree_shift = 0
         self.buffer_rays = self.buffer_rnds = self.buffer_colors = self.cl_screen = 0
@@ -395,7 +406,11 @@ class Scene:
         self.buffer_mats = self.ptb.upload(np.stack(self.mats) if self.mats else np.zeros(0, dtype=MATERIAL))
 
     def _camera(self):
-        return Camera(self.screen_width, self.screen_height, self.global_fov, self.global_yaw, self.global_pitch, self.global_shift)
+        """`Camera cam;` of main.cpp:636: constructing it moves global_shift by the pending interactive motion"""
+        cam, self.global_shift = camera_step(self.screen_width, self.screen_height, self.global_fov, self.global_yaw,
+                                             self.global_pitch, self.global_shift,
+                                             (self.global_forward, self.global_rightward, self.global_upward))
+        return cam
 
     # main.cpp:635-643
     def generate_rays(self):
