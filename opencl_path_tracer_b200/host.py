@@ -469,6 +469,30 @@ class Scene:
         c = self.ptb.read(self.cl_screen, np.float32, self.rays_size * 4)
         return c.reshape(self.screen_height, self.screen_width, 4)
 
+    # ---- headless stand-in for the window: tone-mapped 8-bit PPM and linear PFM of the accumulation buffer
+    def save_ppm(self, path, mode=0):
+        write_ppm(path, self.ptb.resolve_rgba8(self.buffer_colors, self.screen_width, self.screen_height, mode))
+
+    def save_pfm(self, path):
+        write_pfm(path, self.download_colors()[..., :3])
+
+
+def write_ppm(path, rgba8):
+    """binary PPM (P6) from an (H, W, 3|4) uint8 image whose first row is the TOP of the picture"""
+    img = np.ascontiguousarray(np.asarray(rgba8, dtype=np.uint8)[..., :3])
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (img.shape[1], img.shape[0]))
+        f.write(img.tobytes())
+
+
+def write_pfm(path, rgb):
+    """little-endian colour PFM from an (H, W, 3) float32 image whose first row is the BOTTOM of the picture — which
+    is both PFM's convention and the reference's (row 0 = bottom scanline, prog.cl:86-88)"""
+    img = np.ascontiguousarray(np.asarray(rgb, dtype="<f4"))
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (img.shape[1], img.shape[0]))
+        f.write(img.tobytes())
+
 
 # ---------------------------------------------------------------- dumps of the kernel-argument surface
 def load_ptbd(path):

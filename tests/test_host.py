@@ -85,3 +85,14 @@ def test_scene_generators_are_deterministic_and_sized():
     assert 90_000 <= len(a["verts"]) <= 120_000
     g = scenes.describe("small_mixed")
     assert len(g["verts"]) == g["obj_end"][-1] == len(g["tri_mat"])
+
+
+def test_image_writers(tmp_path):
+    rgba = np.arange(2 * 3 * 4, dtype=np.uint8).reshape(2, 3, 4)
+    host.write_ppm(tmp_path / "a.ppm", rgba)
+    raw = (tmp_path / "a.ppm").read_bytes()
+    assert raw.startswith(b"P6\n3 2\n255\n") and raw[11:] == rgba[..., :3].tobytes()
+    rgb = np.linspace(0, 5, 2 * 3 * 3, dtype=np.float32).reshape(2, 3, 3)
+    host.write_pfm(tmp_path / "a.pfm", rgb)
+    raw = (tmp_path / "a.pfm").read_bytes()
+    assert raw.startswith(b"PF\n3 2\n-1.0\n") and np.frombuffer(raw[len(b"PF\n3 2\n-1.0\n"):], dtype="<f4").tolist() == rgb.ravel().tolist()
