@@ -12,12 +12,19 @@
 //   7. k_emit       64-byte traversal nodes holding BOTH children's (inflated) boxes and links;
 //                   a subtree with <= leaf_size triangles becomes one leaf [first, first+count)
 //   8. k_depth      depth of the emitted tree (the traversal stack is bounded; checked by the host)
+//   9. k_flag4 / scan / k_emit4   the same tree collapsed to 4-ary nodes for the wavefront traversal: every
+//                   emitted binary node at EVEN depth becomes a wide node whose slots are its grandchildren
+//                   (a child that is a leaf keeps its slot), compacted by a prefix sum.  Halves the chain of
+//                   dependent node fetches, which is what bounds the traversal (profiles/r01_wf_trace_v2.txt).
 //
 // Node layout (4 x float4, Aila–Laine style):
 //   n0 = (L.lo.x, L.hi.x, L.lo.y, L.hi.y)  n1 = (R.lo.x, R.hi.x, R.lo.y, R.hi.y)
 //   n2 = (L.lo.z, L.hi.z, R.lo.z, R.hi.z)  n3 = (bits(left link), bits(right link), 0, 0)
 // link >= 0: node index.  link < 0: leaf, ~link = (first << 3) | (count-1) in Morton order.
+// Wide node layout (8 x float4 = one 128-byte line): lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] links[4] pad;
+// an empty slot has an all-NaN box, which no slab test accepts.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -215,6 +222,69 @@ __global__ void k_emit(int n, int leaf_size, float eps, const int2 *range, const
     bvh[4 * i + 3] = make_float4(__int_as_float(link[0]), __int_as_float(link[1]), 0.0f, 0.0f);
 }
 
+// ---- 4-ary collapse
+__device__ __forceinline__ bool emitted_node(const int2 *range, int i, int leaf_size) {
+    const int2 rg = range[i];
+    return rg.y - rg.x + 1 > leaf_size || i == 0;
+}
+// flag[i] = 1 iff binary node i is emitted and has an even number of ancestors
+__global__ void k_flag4(int n, int leaf_size, const int2 *range, const int *parent_of_node, int *flag) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int f = 0;
+    if (emitted_node(range, i, leaf_size)) {
+        int depth = 0;
+        for (int a = parent_of_node[i]; a >= 0; a = parent_of_node[a]) depth++;
+        f = (depth & 1) == 0;
+    }
+    flag[i] = f;
+}
+struct Slot { float4 lo, hi; int link; };
+// the traversal link of binary child c (as stored in child[]): leaf, collapsed leaf, or wide node id
+__device__ __forceinline__ bool slot_of(int c, int leaf_size, const int2 *range, const int *id4, const float4 *leaf_lo, const float4 *leaf_hi,
+                                        const float4 *node_lo, const float4 *node_hi, Slot &s) {
+    if (c < 0) { s.lo = leaf_lo[~c]; s.hi = leaf_hi[~c]; s.link = leaf_link(~c, 1); return true; }
+    s.lo = node_lo[c]; s.hi = node_hi[c];
+    const int2 cr = range[c];
+    const int cnt = cr.y - cr.x + 1;
+    if (cnt <= leaf_size) { s.link = leaf_link(cr.x, cnt); return true; }
+    s.link = id4[c];
+    return false;                                      // an emitted internal node
+}
+__global__ void k_emit4(int n, int leaf_size, float eps, const int2 *range, const int2 *child, const int *flag, const int *id4,
+                        const float4 *leaf_lo, const float4 *leaf_hi, const float4 *node_lo, const float4 *node_hi, float4 *bvh4) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1 || !flag[i]) return;
+    Slot s[4];
+    int ns = 0;
+    const int2 c = child[i];
+    const int cc[2] = {c.x, c.y};
+    for (int k = 0; k < 2; ++k) {
+        Slot t;
+        if (slot_of(cc[k], leaf_size, range, id4, leaf_lo, leaf_hi, node_lo, node_hi, t)) { s[ns++] = t; continue; }
+        const int2 g = child[cc[k]];                   // odd-depth internal node: absorbed, its children take the slots
+        const int gg[2] = {g.x, g.y};
+        for (int j = 0; j < 2; ++j) {
+            slot_of(gg[j], leaf_size, range, id4, leaf_lo, leaf_hi, node_lo, node_hi, t);
+            s[ns++] = t;
+        }
+    }
+    const float qnan = __int_as_float(0x7fc00000);
+    float v[6][4];
+    int link[4];
+    for (int k = 0; k < 4; ++k) {
+        const bool on = k < ns;
+        v[0][k] = on ? s[k].lo.x - eps : qnan; v[1][k] = on ? s[k].hi.x + eps : qnan;
+        v[2][k] = on ? s[k].lo.y - eps : qnan; v[3][k] = on ? s[k].hi.y + eps : qnan;
+        v[4][k] = on ? s[k].lo.z - eps : qnan; v[5][k] = on ? s[k].hi.z + eps : qnan;
+        link[k] = on ? s[k].link : leaf_link(0, 1);
+    }
+    float4 *o = bvh4 + 8 * (size_t)id4[i];
+    for (int r = 0; r < 6; ++r) o[r] = make_float4(v[r][0], v[r][1], v[r][2], v[r][3]);
+    o[6] = make_float4(__int_as_float(link[0]), __int_as_float(link[1]), __int_as_float(link[2]), __int_as_float(link[3]));
+    o[7] = make_float4(__int_as_float(ns), 0.0f, 0.0f, 0.0f);
+}
+
 // depth of every triangle's leaf in the EMITTED tree = number of emitted ancestors
 __global__ void k_depth(int n, int leaf_size, const int2 *range, const int *parent_of_node, const int *parent_of_leaf, int *max_depth, int *n_emitted) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
@@ -239,9 +309,28 @@ template <typename T> cudaError_t dalloc(T **p, size_t count) { return cudaMallo
 
 }  // namespace
 
+static cudaTextureObject_t linear_tex(const float4 *p, size_t count) {
+    if (!p || count == 0) return 0;
+    cudaResourceDesc rd;
+    memset(&rd, 0, sizeof rd);
+    rd.resType = cudaResourceTypeLinear;
+    rd.res.linear.devPtr = const_cast<float4 *>(p);
+    rd.res.linear.desc = cudaCreateChannelDesc<float4>();
+    rd.res.linear.sizeInBytes = count * sizeof(float4);
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof td);
+    td.readMode = cudaReadModeElementType;
+    cudaTextureObject_t t = 0;
+    if (cudaCreateTextureObject(&t, &rd, &td, nullptr) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return t;
+}
+
 void lbvh_free(Lbvh *b) {
     if (!b) return;
+    if (b->bvh_tex) cudaDestroyTextureObject(b->bvh_tex);
+    if (b->bvh4_tex) cudaDestroyTextureObject(b->bvh4_tex);
     cudaFree(b->bvh); cudaFree(b->sq0); cudaFree(b->sq1); cudaFree(b->sq2); cudaFree(b->sf0); cudaFree(b->sf1); cudaFree(b->sf2); cudaFree(b->sorted_id);
+    cudaFree(b->bvh4); cudaFree(b->parent); cudaFree(b->flag4); cudaFree(b->id4);
     cudaFree(b->range); cudaFree(b->child); cudaFree(b->leaf_lo); cudaFree(b->leaf_hi); cudaFree(b->node_lo); cudaFree(b->node_hi);
     memset(b, 0, sizeof(*b));
 }
@@ -259,6 +348,12 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
                                                    b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, b->bvh);
         CK(cudaGetLastError());
         b->launches++;
+        if (b->n_nodes4 > 0) {
+            k_emit4<<<(n - 1 + 255) / 256, 256, 0, st>>>(n, b->leaf_size, eps, (const int2 *)b->range, (const int2 *)b->child, b->flag4, b->id4,
+                                                        b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, b->bvh4);
+            CK(cudaGetLastError());
+            b->launches++;
+        }
     }
     return 0;
 }
@@ -276,7 +371,8 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
 
     unsigned *bounds; unsigned long long *keys, *keys2; int *vals, *vals2, *pnode, *pleaf, *arrivals, *stats;
     CK(dalloc(&bounds, 8)); CK(dalloc(&keys, n)); CK(dalloc(&keys2, n)); CK(dalloc(&vals, n)); CK(dalloc(&vals2, n));
-    CK(dalloc(&pnode, n)); CK(dalloc(&pleaf, n)); CK(dalloc(&arrivals, n)); CK(dalloc(&stats, 4));
+    CK(dalloc(&b->parent, n)); CK(dalloc(&b->flag4, n)); CK(dalloc(&b->id4, n + 1)); pnode = b->parent;
+    CK(dalloc(&pleaf, n)); CK(dalloc(&arrivals, n)); CK(dalloc(&stats, 4));
     CK(dalloc(&b->sq0, n)); CK(dalloc(&b->sq1, n)); CK(dalloc(&b->sq2, n)); CK(dalloc(&b->sorted_id, n));
     CK(dalloc(&b->sf0, n)); CK(dalloc(&b->sf1, n)); CK(dalloc(&b->sf2, n));
     CK(dalloc(&b->leaf_lo, n)); CK(dalloc(&b->leaf_hi, n)); CK(dalloc(&b->node_lo, n)); CK(dalloc(&b->node_hi, n));
@@ -313,13 +409,32 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     b->max_depth = hs[0];
     b->n_nodes = n >= 2 ? hs[1] : 0;
     b->root = (n <= b->leaf_size || n < 2) ? ~(((0) << 3) | (n - 1)) : 0;
+    b->n_nodes4 = 0;
+    if (b->root >= 0) {                              // 4-ary collapse: flags, compact ids, node storage
+        k_flag4<<<grid, 256, 0, st>>>(n, b->leaf_size, (const int2 *)b->range, pnode, b->flag4);
+        CK(cudaMemsetAsync(b->flag4 + (n - 1), 0, sizeof(int), st));
+        size_t scan_bytes = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b->flag4, b->id4, n, st));
+        void *scan_tmp;
+        CK(cudaMalloc(&scan_tmp, scan_bytes + 16));
+        CK(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, b->flag4, b->id4, n, st));
+        int total = 0;
+        CK(cudaMemcpyAsync(&total, b->id4 + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        cudaFree(scan_tmp);
+        b->launches += 2;
+        b->n_nodes4 = total;
+        CK(dalloc(&b->bvh4, (size_t)8 * (total > 0 ? total : 1)));
+    }
     if (lbvh_emit(b, 0.0f, st, err, errcap)) return -1;
+    if (n >= 2 && (size_t)4 * n < ((size_t)1 << 27)) b->bvh_tex = linear_tex(b->bvh, (size_t)4 * n);
+    if (b->n_nodes4 > 0 && (size_t)8 * b->n_nodes4 < ((size_t)1 << 27)) b->bvh4_tex = linear_tex(b->bvh4, (size_t)8 * b->n_nodes4);
     CK(cudaEventRecord(e1, st));
     CK(cudaEventSynchronize(e1));
     CK(cudaEventElapsedTime(&b->build_ms, e0, e1));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(pnode); cudaFree(pleaf); cudaFree(arrivals); cudaFree(stats); cudaFree(tmp);
+    cudaFree(pleaf); cudaFree(arrivals); cudaFree(stats); cudaFree(tmp);
     CK(cudaGetLastError());
     return 0;
 }

@@ -28,6 +28,13 @@ namespace PT_NS {
 
 // ---------------------------------------------------------------- small helpers
 PT_DEV float4 ldg4(const float4 *p) { return __ldg(p); }
+// 32 bytes per lane in one instruction (sm_100 LDG.E.256, p 32-byte aligned).  A scattered per-lane fetch costs one L1
+// wavefront per lane and INSTRUCTION, and the LBVH traversal is bound by exactly that (l1tex__throughput 90 %,
+// profiles/r01_wf_trace_v3.txt): fetching a 64-byte node with two loads instead of four halves the L1 work.
+PT_DEV void ldg8(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
 
 struct Work {              // per-thread work counters
     unsigned rays, box, tri, tri1, tri2, tri3, samples;

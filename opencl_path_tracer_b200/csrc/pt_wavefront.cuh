@@ -155,14 +155,21 @@ __global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const in
 }
 
 // ---------------------------------------------------------------- trace: persistent warps over the queue
-enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3 };
+enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 #ifndef WF_FETCH_MIN
 #define WF_FETCH_MIN 8            // refill when this many lanes are idle (or nothing else is runnable)
 #endif
+#ifndef WF_SMEM_STACK
 #define WF_SMEM_STACK 16
+#endif
 
-template <bool COUNT>
-__global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor) {
+// Lane states: FETCH (needs a ray), NODE (link is an inner node), LEAF (link is a leaf), POP (needs the next stack entry).
+// Every warp step votes one phase.  Inside the NODE phase the code is straight-line: the far child is pushed by a
+// predicated store, and ALL lanes that need a stack entry (no child hit, or a leaf just finished) share one pop block
+// that tries two entries per step and drops the culled ones — the first version branched three ways per lane here and
+// spent 47 % of its instructions at fewer than 12 active lanes (profiles/r01_wf_trace_v2.txt).
+template <bool COUNT, bool WIDE>
+__global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor, const int3 tune) {
     const SceneDev &sc = p.sc;
     const int lane = threadIdx.x & 31;
     const int count = *n_in;
@@ -175,19 +182,24 @@ __global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, 
     V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
     Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
     float ix = 0.0f, iy = 0.0f, iz = 0.0f, ox = 0.0f, oy = 0.0f, oz = 0.0f;
+#ifdef WF_DEBUG_STATES
+    unsigned dbgN = 0, dbgL = 0, dbgF = 0, dbgP = 0, dbgI = 0;
+#endif
 #define WF_PUSH(v, d) do { const int2 e_ = make_int2((v), __float_as_int(d)); if (sp < WF_SMEM_STACK) my_stack[sp * PT_BLOCK] = e_; \
                            else if (sp < PT_LBVH_STACK) deep_stack[sp - WF_SMEM_STACK] = e_; ++sp; } while (0)
-#define WF_POP_LIVE(ok) do { ok = false; while (sp > 0) { --sp; const int2 e_ = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK]; \
-                             if (__int_as_float(e_.y) <= best.t) { link = e_.x; ok = true; break; } } } while (0)
 #define WF_FINISH() do { float4 *o_ = p.wf_ray1 + path; o_->z = best.t; o_->w = __int_as_float(best.tri); st = WF_FETCH; } while (0)
     for (;;) {
         if (exhausted && st == WF_FETCH) st = WF_EXIT;
         const unsigned bF = __ballot_sync(0xffffffffu, st == WF_FETCH);
-        const unsigned bN = __ballot_sync(0xffffffffu, st == WF_NODE);
+        const unsigned bN = __ballot_sync(0xffffffffu, st == WF_NODE || st == WF_POP);
         const unsigned bL = __ballot_sync(0xffffffffu, st == WF_LEAF);
         if ((bF | bN | bL) == 0u) break;
         const int cF = __popc(bF), cN = __popc(bN), cL = __popc(bL);
-        if (cF > 0 && (cF >= WF_FETCH_MIN || (bN | bL) == 0u)) {
+#ifdef WF_DEBUG_STATES   // throw-away instrumentation: lane-state census per vote, reported through the work counters
+        { const int cP = __popc(__ballot_sync(0xffffffffu, st == WF_POP)); dbgN += cN; dbgL += cL; dbgF += cF; dbgP += cP; dbgI += 1; }
+#endif
+        // tune.x: idle lanes that trigger a refill, tune.y: lanes at a leaf that trigger a leaf step, tune.z: node steps per vote
+        if (cF > 0 && (cF >= tune.x || (bN | bL) == 0u)) {
             // ------------------------------------------------------------ FETCH: one atomic for the whole warp
             int base = 0;
             if (lane == (__ffs(bF) - 1)) base = atomicAdd(cursor, cF);
@@ -209,13 +221,53 @@ __global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, 
                     st = WF_EXIT;
                 }
             }
-        } else if (cN >= cL) {
+        } else if (cN > 0 && cL < tune.y) {
             // ------------------------------------------------------------ NODE steps
 #pragma unroll 1
-            for (int k = 0; k < PT_SCHED_NODE_STEPS; ++k) {
-                if (st == WF_NODE) {
+            for (int k = 0; k < tune.z; ++k) {
+                if (WIDE && st == WF_NODE) {
+                    // 4-ary node (lbvh.cu): four slab tests, hits sorted by entry distance, nearest visited, rest pushed far-to-near
+                    const float4 *nd = sc.bvh4 + 8 * (size_t)link;
+                    float4 X0, X1, Y0, Y1, Z0, Z1, LK, pad_;
+                    if (sc.bvh4_tex) {
+                        const int t_ = 8 * link;
+                        X0 = tex1Dfetch<float4>(sc.bvh4_tex, t_); X1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 1);
+                        Y0 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2); Y1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 3);
+                        Z0 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4); Z1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 5);
+                        LK = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 6);
+                    } else {
+                        ldg8(nd, X0, X1); ldg8(nd + 2, Y0, Y1); ldg8(nd + 4, Z0, Z1); ldg8(nd + 6, LK, pad_);
+                    }
+                    if (COUNT) wk.box += 4;
+                    float d0, d1, d2, d3;
+#define WF_SLAB(dk, c) do { float a_ = fmaf(X0.c, ix, -ox), b_ = fmaf(X1.c, ix, -ox); float l0_ = fminf(a_, b_), l1_ = fmaxf(a_, b_);          \
+                            a_ = fmaf(Y0.c, iy, -oy); b_ = fmaf(Y1.c, iy, -oy); l0_ = fmaxf(l0_, fminf(a_, b_)); l1_ = fminf(l1_, fmaxf(a_, b_)); \
+                            a_ = fmaf(Z0.c, iz, -oz); b_ = fmaf(Z1.c, iz, -oz); l0_ = fmaxf(l0_, fminf(a_, b_)); l1_ = fminf(l1_, fmaxf(a_, b_)); \
+                            const float e_ = l0_ * 0.999996f;                                                                                 \
+                            dk = ((l0_ <= l1_ * 1.000004f) & (l1_ >= 0.0f) & (e_ <= best.t)) ? e_ : PT_NO_HIT; } while (0)
+                    WF_SLAB(d0, x); WF_SLAB(d1, y); WF_SLAB(d2, z); WF_SLAB(d3, w);
+#undef WF_SLAB
+                    int k0 = __float_as_int(LK.x), k1 = __float_as_int(LK.y), k2 = __float_as_int(LK.z), k3 = __float_as_int(LK.w);
+#define WF_CE(da, ka, db, kb) do { const bool sw_ = db < da; const float td_ = sw_ ? db : da; const int tk_ = sw_ ? kb : ka; \
+                                   db = sw_ ? da : db; kb = sw_ ? ka : kb; da = td_; ka = tk_; } while (0)
+                    WF_CE(d0, k0, d1, k1); WF_CE(d2, k2, d3, k3); WF_CE(d0, k0, d2, k2); WF_CE(d1, k1, d3, k3); WF_CE(d1, k1, d2, k2);
+#undef WF_CE
+                    if (d3 < PT_NO_HIT) WF_PUSH(k3, d3);
+                    if (d2 < PT_NO_HIT) WF_PUSH(k2, d2);
+                    if (d1 < PT_NO_HIT) WF_PUSH(k1, d1);
+                    link = k0;
+                    st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
+                }
+                if (!WIDE && st == WF_NODE) {
                     const float4 *nd = sc.bvh + 4 * (size_t)link;
-                    const float4 n0 = ldg4(nd), n1 = ldg4(nd + 1), n2 = ldg4(nd + 2), n3 = ldg4(nd + 3);
+                    float4 n0, n1, n2, n3;
+                    if (sc.bvh_tex) {
+                        const int t_ = 4 * link;
+                        n0 = tex1Dfetch<float4>(sc.bvh_tex, t_); n1 = tex1Dfetch<float4>(sc.bvh_tex, t_ + 1);
+                        n2 = tex1Dfetch<float4>(sc.bvh_tex, t_ + 2); n3 = tex1Dfetch<float4>(sc.bvh_tex, t_ + 3);
+                    } else {
+                        ldg8(nd, n0, n1); ldg8(nd + 2, n2, n3);
+                    }
                     if (COUNT) wk.box += 2;
                     float a, b, l0, l1, r0, r1;
                     a = fmaf(n0.x, ix, -ox); b = fmaf(n0.y, ix, -ox); l0 = fminf(a, b); l1 = fmaxf(a, b);
@@ -224,21 +276,29 @@ __global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, 
                     a = fmaf(n1.x, ix, -ox); b = fmaf(n1.y, ix, -ox); r0 = fminf(a, b); r1 = fmaxf(a, b);
                     a = fmaf(n1.z, iy, -oy); b = fmaf(n1.w, iy, -oy); r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
                     a = fmaf(n2.z, iz, -oz); b = fmaf(n2.w, iz, -oz); r0 = fmaxf(r0, fminf(a, b)); r1 = fminf(r1, fmaxf(a, b));
-                    const bool hl = (l0 <= l1 * 1.000004f) & (l1 >= 0.0f) & (l0 * 0.999996f <= best.t);
-                    const bool hr = (r0 <= r1 * 1.000004f) & (r1 >= 0.0f) & (r0 * 0.999996f <= best.t);
+                    const float l0e = l0 * 0.999996f, r0e = r0 * 0.999996f;
+                    const bool hl = (l0 <= l1 * 1.000004f) & (l1 >= 0.0f) & (l0e <= best.t);
+                    const bool hr = (r0 <= r1 * 1.000004f) & (r1 >= 0.0f) & (r0e <= best.t);
                     const int ll = __float_as_int(n3.x), lr = __float_as_int(n3.y);
-                    if (hl & hr) {
-                        const bool left_first = l0 <= r0;
-                        WF_PUSH(left_first ? lr : ll, (left_first ? r0 : l0) * 0.999996f);
-                        link = left_first ? ll : lr;
-                    } else if (hl | hr) {
-                        link = hl ? ll : lr;
-                    } else {
-                        bool ok;
-                        WF_POP_LIVE(ok);
-                        if (!ok) WF_FINISH();
+                    const bool right_first = hr & (!hl | (r0 < l0));          // both hit: the nearer entry first, left on ties
+                    const int near_link = right_first ? lr : ll, far_link = right_first ? ll : lr;
+                    if (hl & hr) WF_PUSH(far_link, right_first ? l0e : r0e);
+                    link = near_link;
+                    st = (hl | hr) ? (near_link >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
+                }
+                if (st == WF_POP) {
+#pragma unroll
+                    for (int attempt = 0; attempt < 2; ++attempt) {
+                        if (st == WF_POP) {
+                            if (sp == 0) {
+                                WF_FINISH();
+                            } else {
+                                --sp;
+                                const int2 e = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK];
+                                if (__int_as_float(e.y) <= best.t) { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
+                            }
+                        }
                     }
-                    if (st == WF_NODE && link < 0) st = WF_LEAF;
                 }
             }
         } else {
@@ -255,12 +315,15 @@ __global__ void __launch_bounds__(PT_BLOCK, 6) k_wf_trace(const RenderParams p, 
                         if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
                     }
                 }
-                bool ok;
-                WF_POP_LIVE(ok);
-                if (!ok) WF_FINISH(); else st = link >= 0 ? WF_NODE : WF_LEAF;
+                st = WF_POP;
             }
         }
     }
+#undef WF_PUSH
+#undef WF_FINISH
+#ifdef WF_DEBUG_STATES
+    if (COUNT) { const bool l0_ = lane == 0; wk.box = l0_ ? dbgP : 0; wk.tri = 0; wk.tri1 = l0_ ? dbgN : 0; wk.tri2 = l0_ ? dbgL : 0; wk.tri3 = l0_ ? dbgF : 0; wk.samples = l0_ ? dbgI : 0; }
+#endif
     wf_flush_counters(p, wk, COUNT);
 }
 
@@ -274,7 +337,8 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     int sms = 148, dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int trace_blocks = sms * 6;
+    static const int per_sm = getenv("PTB_WF_BLOCKS") ? atoi(getenv("PTB_WF_BLOCKS")) : 9;   // 56 registers, 16 KB stack: 9 fit; measured 1.98 (6) / 2.10 (8) / 2.11 (9) Grays/s
+    const int trace_blocks = sms * per_sm;
     const long long max_iters = (long long)p.spp * (p.iterations > 0 ? p.iterations : 0);
     int host_count = n;
     for (long long it = 0; it < max_iters; ++it) {
@@ -282,8 +346,17 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
         // next queue length and the fetch cursor start at zero
         cudaMemsetAsync(p.wf_ctrl + b, 0, sizeof(int), st);
         cudaMemsetAsync(p.wf_ctrl + 2, 0, sizeof(int), st);
-        if (p.count_work) k_wf_trace<true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2);
-        else k_wf_trace<false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2);
+        const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+        static const int3 tune = make_int3(getenv("PTB_WF_FETCH_MIN") ? atoi(getenv("PTB_WF_FETCH_MIN")) : WF_FETCH_MIN,
+                                           getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 8,
+                                           getenv("PTB_WF_NODE_STEPS") ? atoi(getenv("PTB_WF_NODE_STEPS")) : PT_SCHED_NODE_STEPS);
+        if (p.count_work) {
+            if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
+            else k_wf_trace<true, false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
+        } else {
+            if (wide) k_wf_trace<false, true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
+            else k_wf_trace<false, false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
+        }
         k_wf_shade<<<(host_count + 255) / 256, 256, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_queue[b], p.wf_ctrl + b);
         launches += 2;
         if ((it & 15) == 15) {                     // every 16 iterations: learn the real queue length (shrinks the grids, ends early)

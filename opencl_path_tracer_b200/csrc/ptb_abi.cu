@@ -83,6 +83,8 @@ struct State {
     int sum_mode = 0, count_work = 0;
     int lbvh_leaf = 4;
     int merge_prims = 1;
+    int tex_nodes = 1;                 // node fetches through the texture pipe (PTB_TEX_NODES=0: LSU)
+    int wide_bvh = 1;                  // wavefront traversal over the 4-ary collapse of the LBVH (PTB_WIDE_BVH=0: binary)
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
     unsigned long long *counters = nullptr;
     unsigned long long launches = 0;
@@ -287,6 +289,11 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         rc = ensure_lbvh(reach);
         if (rc) return rc;
         p.sc.bvh = s.lbvh.bvh;
+        p.sc.bvh_tex = G.tex_nodes ? s.lbvh.bvh_tex : 0;
+        p.sc.bvh4_tex = G.tex_nodes ? s.lbvh.bvh4_tex : 0;
+        // the 4-ary traversal pushes up to 3 entries per level: usable when the stack bound (64) covers the tree
+        const int wide_levels = (s.lbvh.max_depth + 1) / 2;
+        p.sc.bvh4 = (G.wide_bvh && s.lbvh.n_nodes4 > 0 && 3 * wide_levels + 1 <= 64) ? s.lbvh.bvh4 : nullptr;
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
     }
@@ -390,6 +397,8 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_LBVH_LEAF"))) G.lbvh_leaf = atoi(env);
     if ((env = getenv("PTB_BRUTE_MAX"))) G.brute_max = atoi(env);
     if ((env = getenv("PTB_MERGE_PRIMS"))) G.merge_prims = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     return PTB_SUCCESS;
 }
 

@@ -3,7 +3,7 @@
 usage: python profiles/ncu_regions.py rep.ncu-rep [min_pct]"""
 import csv, subprocess, sys
 rep = sys.argv[1]; minpct = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--launch-count", "1"], capture_output=True, text=True).stdout   # first kernel of the report
 rows = list(csv.reader(out.splitlines()))
 hdr = rows[1]
 ia, isrc, ie, it, isamp = (hdr.index(k) for k in ("Address", "Source", "Instructions Executed", "Avg. Threads Executed", "# Samples"))
