@@ -22,6 +22,8 @@ import time
 
 import numpy as np
 
+EMIT = print          # replaced by _QuietStdout.emit when run as a script
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -160,7 +162,7 @@ def reference_arm(args, W, H, depth, scene_name, workload):
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    EMIT(json.dumps(line))
 
 
 # ---------------------------------------------------------------- our arm
@@ -353,10 +355,33 @@ def main():
                        "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
         }
-        print(json.dumps(line))
+        EMIT(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
+class _QuietStdout:
+    """The contract is ONE JSON line on stdout: while the bench runs, file descriptor 1 points at stderr so that library
+    chatter (NCCL's version banner, torchrun notices) cannot land in front of it; `emit` writes to the real stdout."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def emit(self, text):
+        sys.stdout.flush()
+        os.write(self.saved, (text + "\n").encode())
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        return False
+
+
 if __name__ == "__main__":
-    main()
+    with _QuietStdout() as _out:
+        EMIT = _out.emit
+        main()
