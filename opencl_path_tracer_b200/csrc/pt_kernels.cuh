@@ -20,6 +20,7 @@
 #error "define PT_NS"
 #endif
 
+#include <stdio.h>
 #include <stdlib.h>
 #include "pt_math.cuh"
 #include "pt_params.h"
@@ -365,9 +366,12 @@ PT_DEV void orthonormal_base(V3 v1, V3 &v2, V3 &v3o) {
     }
     v3o = cross(v1, v2);
 }
-PT_DEV void new_ray_diffuse(V3 hitP, V3 N, float rnd1, float rnd2, V3 &P, V3 &D) {
+// frame: optional precomputed (X, Z) of the UNFLIPPED stored normal (prims.cu); flipped: N is its negation, for which
+// orthonormal_base yields (X, -Z)
+PT_DEV void new_ray_diffuse(V3 hitP, V3 N, float rnd1, float rnd2, V3 &P, V3 &D, const V3 *frame = nullptr, bool flipped = false) {
     V3 X, Y = N, Z;
-    orthonormal_base(Y, Z, X);
+    if (frame) { X = frame[0]; Z = flipped ? -frame[1] : frame[1]; }
+    else orthonormal_base(Y, Z, X);
     float r = pt_sqrt(rnd1);
     float c, s;
     pt_disk_angle(rnd2, c, s);
@@ -407,17 +411,20 @@ PT_DEV void path_reset(Path &p) {
 
 // One iteration of the bounce loop body after a hit (prog.cl:321-366).  hitN is the stored
 // triangle normal (unflipped).  Updates the ray and the path state.
-PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32_t &rng, Path &ps, V3 eye, int iterations) {
+template <bool NONNEG = false>
+PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32_t &rng, Path &ps, V3 eye, int iterations,
+                      const V3 *frame = nullptr) {
     if (iterations == 1) ps.color = m.kd + m.emission;                       // flat preview, prog.cl:323-325
     V3 N = hitN;
-    if (dot(rayD, N) > 0.0f) N = -N;                                        // prog.cl:326-328
+    const bool flipped = dot(rayD, N) > 0.0f;
+    if (flipped) N = -N;                                                    // prog.cl:326-328
     if (m.type == 0 || m.type == 3) {
         // diffuse + Phong lobe (prog.cl:329-340) and emitter (prog.cl:358-366) share the cosine-weighted
         // bounce, so the warp stays converged through the sampling code
         const float intensity = pt_fmax(0.0f, dot(-rayD, N));               // emitter only: uses the OLD ray
-        float r1 = pt_rand(rng), r2 = pt_rand(rng);
+        float r1 = pt_rand_t<NONNEG>(rng), r2 = pt_rand_t<NONNEG>(rng);
         V3 nP, nD;
-        new_ray_diffuse(hitP, N, r1, r2, nP, nD);
+        new_ray_diffuse(hitP, N, r1, r2, nP, nD, frame, flipped);
         if (m.type == 0) {
             float cos_theta = dot(nD, N);
             ps.fL = ps.fL * (m.kd * pt_fmax(0.0f, cos_theta));
@@ -440,7 +447,7 @@ PT_DEV void shade_hit(const Mat &m, V3 hitP, V3 hitN, V3 &rayP, V3 &rayD, uint32
     } else if (m.type == 2) {                                               // glass, prog.cl:346-357 + 228-245
         V3 oldD = rayD;
         bool before = ps.in;
-        float rnd = pt_rand(rng);
+        float rnd = pt_rand_t<NONNEG>(rng);
         float n = ps.in ? 1.0f / m.n : m.n;
         float cosa = dot(-oldD, N);
         float disc = 1.0f - pt_div(pt_div(1.0f - cosa * cosa, n), n);
@@ -477,7 +484,8 @@ PT_DEV float4 reinhard_tone_map(V3 c) {
 #define PT_BLOCK 128
 #define PT_SMEM_MAX_TRIS 4096   // 192 KB of triangles at most in shared memory
 
-template <int ACCEL, bool COUNT, int SMEM, int MINB, int U>
+// NONNEG: the launch is known to start from RNG states in [0, 2^31) (see pt_rand_nonneg)
+template <int ACCEL, bool COUNT, int SMEM, int MINB, int U, bool NONNEG>
 __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p) {
     extern __shared__ float4 s_tris[];
     const SceneDev &sc = p.sc;
@@ -523,6 +531,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
             s_tris[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
             s_tris[7 * j + 6] = make_float4(-sa.x, -sb.x, -sa.y, -sb.y);
         }
+        for (int j = threadIdx.x; j < 3 * sc.n_prims; j += PT_BLOCK) s_tris[7 * n_prim_pairs + j] = ldg4(sc.prim_shade + j);
         __syncthreads();
     }
 #endif
@@ -558,7 +567,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
                 const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
                 rayP = v3(r[0]); rayD = v3(r[1]);
             } else {                                             // gen_ray fused, prog.cl:384-389
-                float r1 = pt_rand(rng), r2 = pt_rand(rng);
+                float r1 = pt_rand_t<NONNEG>(rng), r2 = pt_rand_t<NONNEG>(rng);
                 camera_ray(p, cam_x, cam_y, r1, r2, rayP, rayD);
             }
             path_reset(ps);
@@ -573,8 +582,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
 #if !PT_PARITY
             if (SMEM == 2) brute_smem_pairs<U>(s_tris, (sc.n_tris + 1) >> 1, rayP, rayD, best); else
             if (SMEM == 3) {
-                brute_smem_prims<U>(s_tris, n_prim_pairs, rayP, rayD, best);
-                if (best.t < PT_NO_HIT) best.tri = __ldg(sc.prim_rep + best.tri);
+                brute_smem_prims<U>(s_tris, n_prim_pairs, rayP, rayD, best);     // best.tri = primitive index
             } else
 #endif
             if (SMEM == 1) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
@@ -589,9 +597,20 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
             if (trace && best.t < PT_NO_HIT) {
                 // Hit record of triangle_intersect (prog.cl:107): p = P + V*t, N = tri->N, mati
                 V3 hitP = rayP + rayD * best.t;
-                V3 hitN = tri_normal(ldg4(sc.q0 + best.tri), ldg4(sc.q1 + best.tri), ldg4(sc.q2 + best.tri));
-                Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
-                shade_hit(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
+#if !PT_PARITY
+                if (SMEM == 3) {                                 // normal, material and tangent frame of the primitive from shared memory
+                    const float4 *sh = s_tris + 7 * n_prim_pairs + 3 * best.tri;
+                    const float4 h0 = sh[0];
+                    const V3 frame[2] = {v3(sh[1]), v3(sh[2])};
+                    Mat m = load_material(sc.mats, __float_as_int(h0.w));
+                    shade_hit<NONNEG>(m, hitP, v3(h0), rayP, rayD, rng, ps, eye, p.iterations, frame);
+                } else
+#endif
+                {
+                    V3 hitN = tri_normal(ldg4(sc.q0 + best.tri), ldg4(sc.q1 + best.tri), ldg4(sc.q2 + best.tri));
+                    Mat m = load_material(sc.mats, (int)__ldg(sc.mati + best.tri));
+                    shade_hit<NONNEG>(m, hitP, hitN, rayP, rayD, rng, ps, eye, p.iterations);
+                }
                 if (++depth >= p.iterations) alive = false;
             } else {
                 alive = false;                                   // miss: break, prog.cl:367-376
@@ -643,16 +662,16 @@ __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n)
 }
 
 // ---------------------------------------------------------------- host-side dispatch
-template <int ACCEL, bool COUNT, int SMEM, int MINB = 1, int U = 2>
+template <int ACCEL, bool COUNT, int SMEM, int MINB = 1, int U = 2, bool NONNEG = false>
 static void launch_one(const RenderParams &p, cudaStream_t st) {
     dim3 grid((p.W + 15) / 16, (p.H + 7) / 8);
     size_t smem = 0;
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 1) smem = (size_t)p.sc.n_tris * 3 * sizeof(float4);
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) smem = (size_t)((p.sc.n_tris + 1) / 2) * 6 * sizeof(float4);
-    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) smem = (size_t)((p.sc.n_prims + 1) / 2) * 7 * sizeof(float4);
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) smem = ((size_t)((p.sc.n_prims + 1) / 2) * 7 + 3 * (size_t)p.sc.n_prims) * sizeof(float4);
     if (smem > 48 * 1024)
-        cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM, MINB, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_render<ACCEL, COUNT, SMEM, MINB, U><<<grid, PT_BLOCK, smem, st>>>(p);
+        cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM, MINB, U, NONNEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_render<ACCEL, COUNT, SMEM, MINB, U, NONNEG><<<grid, PT_BLOCK, smem, st>>>(p);
 }
 
 void launch_render(const RenderParams &p, cudaStream_t st) {
@@ -662,7 +681,12 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
         if (smem) {
             if (c) launch_one<PT_ACCEL_BRUTE, true, 1>(p, st);
 #if !PT_PARITY
-            else if (p.sc.n_prims > 0) launch_one<PT_ACCEL_BRUTE, false, 3, 8, 4>(p, st);   // same scan over merged convex quads (prims.cu)
+            else if (p.sc.n_prims > 0) {                              // same scan over merged convex quads (prims.cu)
+                static const bool verbose = getenv("PTB_VERBOSE") != nullptr;
+                if (verbose) fprintf(stderr, "ptb: k_render scan over %d primitives, rng_nonneg=%d\n", p.sc.n_prims, p.rng_nonneg);
+                if (p.rng_nonneg) launch_one<PT_ACCEL_BRUTE, false, 3, 8, 4, true>(p, st);
+                else launch_one<PT_ACCEL_BRUTE, false, 3, 8, 4>(p, st);
+            } else if (p.rng_nonneg) launch_one<PT_ACCEL_BRUTE, false, 2, 8, 4, true>(p, st);
             else launch_one<PT_ACCEL_BRUTE, false, 2, 8, 4>(p, st);   // packed-FP32 pair scan; 64 registers -> 8 blocks/SM, 4 pairs in flight
                                                                       // (measured best of 8 (occupancy, unroll) variants: 23.0 vs 20.7 Grays/s)
 #else

@@ -91,5 +91,16 @@ PT_DEV float pt_rand(uint32_t &state) {
     state = r;
     return __uint2float_rn(r) * 4.656612873077392578125e-10f;  // * 2^-31
 }
+// The same step for a state KNOWN to lie in [0, 2^31): every state the generator itself produces, and every seed the
+// reference host uploads (main.cpp:522-526).  The C-ABI verifies the uploaded buffer once (ptb_abi.cu, k_any_negative)
+// before it launches a kernel built on this variant; the generic function above stays the default.
+PT_DEV float pt_rand_nonneg(uint32_t &state) {
+    const uint64_t n = (uint64_t)state * 48271ull;
+    uint32_t r = (uint32_t)(n & 0x7fffffffull) + (uint32_t)(n >> 31);
+    if (r >= 0x7fffffffu) r -= 0x7fffffffu;
+    state = r;
+    return __uint2float_rn(r) * 4.656612873077392578125e-10f;
+}
+template <bool NONNEG> PT_DEV float pt_rand_t(uint32_t &state) { return NONNEG ? pt_rand_nonneg(state) : pt_rand(state); }
 
 #endif  // PT_MATH_CUH_

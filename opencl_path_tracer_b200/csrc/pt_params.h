@@ -39,6 +39,7 @@ struct SceneDev {
     // merged scan primitives for the fast brute-force scan (prims.cu); n_prims == 0: not built / nothing merged
     const float4 *pq0, *pq1, *pq2;// fast layout
     const float2 *prim_ab;        // edge slopes (b, a) of the quad's two far edges; (1, 0) for a lone triangle
+    const float4 *prim_shade;     // 3 per primitive: (N, bits(mati)) (X, 0) (Z, 0) — normal, material, tangent frame
     const int *prim_rep;          // primitive → upload index of the triangle that stands for it
     int n_prims;
 };
@@ -62,6 +63,7 @@ struct RenderParams {
     int sum_mode;                 // 1: colors += sample (spp-split), 0: running mean (prog.cl:379)
     int accel;                    // PT_ACCEL_*
     int count_work;               // 1: also count box / triangle tests
+    int rng_nonneg;               // 1: every RNG state of this launch was verified to lie in [0, 2^31) (pt_rand_nonneg)
     unsigned long long *counters; // PT_CNT_WORDS words
     // wavefront pipeline scratch (pt_wavefront.cuh), one path per pixel, allocated by ptb_abi.cu; null = megakernel only
     float4 *wf_ray0, *wf_ray1;    // (P.xyz, D.x) (D.y, D.z, t_hit, bits(tri))

@@ -34,6 +34,10 @@ struct MemObj {
     bool image = false;
     int w = 0, h = 0;
     unsigned long long version = 0;   // bumped by every write: invalidates staged copies
+    // RNG-state buffers: version + 1 at which the first `seeds_checked` ints were scanned, and what the scan found
+    unsigned long long seeds_version = 0;
+    size_t seeds_checked = 0;
+    bool seeds_nonneg = false;
 };
 
 struct Arg {
@@ -56,6 +60,7 @@ struct Staged {                        // device-internal copy of the scene, val
     // merged scan primitives (prims.cu), built on first use by a fast brute-force launch
     float4 *p0 = nullptr, *p1 = nullptr, *p2 = nullptr;
     float2 *prim_ab = nullptr;
+    float4 *prim_shade = nullptr;
     int *prim_rep = nullptr, *n_prims_dev = nullptr;
     int n_prims = 0;
     bool prims_valid = false;
@@ -159,6 +164,37 @@ __global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 
     f2[i] = make_float4((float)mu[2], (float)mv[0], (float)mv[1], (float)mv[2]);
 }
 
+// 1 into *flag if any of the n ints is negative
+__global__ void k_any_negative(const int *v, size_t n, int *flag) {
+    bool neg = false;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) neg |= v[i] < 0;
+    if (__any_sync(0xffffffffu, neg) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
+// Are the first n RNG states of this buffer all in [0, 2^31)?  True for every seed the reference host uploads and for
+// every state the kernels write back, so one scan per host write decides whether launches may use the kernels built on
+// pt_rand_nonneg (pt_math.cuh).
+int seeds_nonneg(MemObj *rnds, size_t n, bool *out) {
+    *out = false;
+    // memory owned by someone else (ptb_wrap_device: a torch tensor, an NCCL buffer) can change behind our back: rescan per launch
+    if (!rnds->owned || rnds->seeds_version != rnds->version + 1 || rnds->seeds_checked < n) {
+        if (!G.counters) return PTB_SUCCESS;
+        int *flag = reinterpret_cast<int *>(G.counters + PT_CNT_WORDS);      // spare word behind the work counters
+        CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), G.stream));
+        k_any_negative<<<592, 256, 0, G.stream>>>((const int *)rnds->dptr, n, flag);
+        CUDA_OK(cudaGetLastError());
+        G.launches++;
+        int h = 1;
+        CUDA_OK(cudaMemcpyAsync(&h, flag, sizeof h, cudaMemcpyDeviceToHost, G.stream));
+        CUDA_OK(cudaStreamSynchronize(G.stream));
+        rnds->seeds_version = rnds->version + 1;
+        rnds->seeds_checked = n;
+        rnds->seeds_nonneg = h == 0;
+    }
+    *out = rnds->seeds_nonneg;
+    return PTB_SUCCESS;
+}
+
 int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
     Staged &s = G.staged;
     if (s.tris_handle == handle && s.tris_version == tris->version && s.n_tris == n_tris) return PTB_SUCCESS;
@@ -203,10 +239,11 @@ int ensure_prims() {
         CUDA_OK(cudaMalloc((void **)&s.p1, PRIMS_MAX_TRIS * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.p2, PRIMS_MAX_TRIS * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.prim_ab, PRIMS_MAX_TRIS * sizeof(float2)));
+        CUDA_OK(cudaMalloc((void **)&s.prim_shade, 3 * PRIMS_MAX_TRIS * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.prim_rep, PRIMS_MAX_TRIS * sizeof(int)));
         CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
     }
-    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.n_prims_dev, G.stream);
+    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.prim_shade, s.n_prims_dev, G.stream);
     CUDA_OK(cudaGetLastError());
     G.launches++;
     int n = 0;
@@ -275,7 +312,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
         rc = ensure_prims();
         if (rc) return rc;
-        p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_ab = s.prim_ab; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
+        p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_ab = s.prim_ab; p.sc.prim_shade = s.prim_shade; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
     }
     p.sc.mats = (const RefMaterial *)mats->dptr;
     p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
@@ -308,6 +345,12 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.sum_mode = G.sum_mode;
     p.count_work = G.count_work;
     p.counters = G.counters;
+    if (fastm && !from_rays) {                       // (a two-kernel host may hand trace_ray states gen_ray never saw)
+        bool ok_seeds = false;
+        rc = seeds_nonneg(rnds, npix, &ok_seeds);
+        if (rc) return rc;
+        p.rng_nonneg = ok_seeds ? 1 : 0;
+    }
     pt_cam_affine(p);
     return PTB_SUCCESS;
 }
@@ -387,8 +430,8 @@ int ptb_init(int device_ordinal) {
     CUDA_OK(cudaGetDeviceProperties(&G.prop, dev));
     CUDA_OK(cudaStreamCreateWithFlags(&G.own_stream, cudaStreamNonBlocking));
     G.stream = G.own_stream;
-    CUDA_OK(cudaMalloc((void **)&G.counters, PT_CNT_WORDS * sizeof(unsigned long long)));
-    CUDA_OK(cudaMemset(G.counters, 0, PT_CNT_WORDS * sizeof(unsigned long long)));
+    CUDA_OK(cudaMalloc((void **)&G.counters, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
+    CUDA_OK(cudaMemset(G.counters, 0, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
     G.device = dev;
     G.inited = true;
     const char *env;
@@ -411,7 +454,7 @@ int ptb_shutdown(void) {
     G.mems.clear();
     Staged &s = G.staged;
     cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
-    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
+    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_shade); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
     lbvh_free(&s.lbvh);
     s = Staged();
     cudaFree(G.counters);

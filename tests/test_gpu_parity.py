@@ -283,3 +283,38 @@ def test_device_ingested_scene_renders_like_host_scene(ptb, cornell_ref):
     ptb.finish()
     st = util.compare(s.download_colors(), cornell_ref["colors"])
     assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+
+
+# ---------------------------------------------------------------- RNG states outside [0, 2^31)
+@pytest.mark.parametrize("math", [capi.MATH_PARITY, capi.MATH_FAST])
+def test_negative_rng_states_follow_the_reference_conversion(ptb, cornell_ref, math):
+    """`(ulong)seed` of a NEGATIVE int sign-extends (prog.cl:73): such states never come from the reference host, but the
+    buffer is host-writable, so the kernels must follow the conversion.  The fast flavour's branch-free generator
+    (pt_rand_nonneg) may only be selected after the C-ABI has scanned the uploaded states — this is the test of that scan."""
+    from oracle import pt_oracle_py as po
+    surf = host.load_ptbd(cornell_ref["files"]["dump"])
+    seeds = host.minstd_rand0_seeds(W * H).astype(np.int32)
+    seeds[::7] = -seeds[::7]
+    seeds[3] = -2147483648
+    orc = po.OracleScene(surf, brute=True, seeds=seeds.copy())
+    want = orc.render(SPP).copy()
+    ptb.set_accel(capi.ACCEL_BRUTE); ptb.set_math(math); ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    s = host.scene_from_surface(surf, ptb)
+    ptb.write(s.buffer_rnds, seeds)
+    s.render_spp(SPP)
+    ptb.finish()
+    got, rnds = s.download_colors(), s.download_rnds()
+    st = util.compare(got, want)
+    if math == capi.MATH_PARITY:
+        assert st["bit_equal_frac"] >= 1.0 - 1e-5, st
+        assert (rnds == orc.rnds).mean() >= 1.0 - 1e-5
+    else:
+        assert st["frac_rel_le_1e-4"] >= 0.999 and st["rmse_over_mean"] <= 0.01, st
+        assert (rnds == orc.rnds).mean() >= 0.999
+    # and the same scene object, re-seeded with valid states, is back on the fast generator with the right image
+    ptb.write(s.buffer_rnds, host.minstd_rand0_seeds(W * H))
+    s.current_sample = 0
+    s.render_spp(SPP)
+    ptb.finish()
+    st = util.compare(s.download_colors(), cornell_ref["colors"])
+    assert st["frac_rel_le_1e-4"] >= 0.999, st
