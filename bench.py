@@ -23,6 +23,8 @@ import time
 import numpy as np
 
 EMIT = print          # replaced by _QuietStdout.emit when run as a script
+# measured once under ncu (never inside a timed run): DRAM bytes of one launch of the dominant kernel, per workload
+NCU_DRAM_BYTES_PER_LAUNCH = {"cornell_1080p_1024spp_d4": 32.8e6}   # 8.35 MB read + 24.46 MB written
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -320,7 +322,9 @@ def main():
         per_gpu_rays_s = total_rays / world / (total_ms * 1e-3)
         achieved = f_ray * per_gpu_rays_s / 1e12
         roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                "traffic": None, "kernel": "k_render (fused gen_ray + trace_ray + accumulate)",
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, "
+                "ncu --set full (profiles/r01_render_v7.txt); per launch, independent of spp: the per-pixel state is touched once",
+                "kernel": "k_render (fused gen_ray + trace_ray + accumulate)",
                 "peak_source": f"{sms} SMs x 128 FP32 lanes x 2 x {sm_max:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); the path has no dense contraction "
                                "and ~0 mandatory HBM traffic, so neither the hbm nor the tensor roofline bounds it (SURVEY 8d)",
                 "numerator": "algorithmic flops of the reference's closest-hit search for this scene (counting pass over the plain triangles); "
