@@ -56,16 +56,7 @@ static_assert(sizeof(RefBBox) == 32, "BBox ABI");
 //   q0[i] = (r1.x, r1.y, r1.z, N.x)   q1[i] = (r2.x, r2.y, r2.z, N.y)   q2[i] = (r3.x, r3.y, r3.z, N.z)
 // mati[i] is a separate uint16 array touched once per ray (for the winning triangle only).
 //
-// LBVH node (32 B, two float4): children boxes are NOT stored in the parent; each node carries
-// its own box and its two child links, so one 32-byte fetch yields box + links:
-//   lo = (min.x, min.y, min.z, bits(left))   hi = (max.x, max.y, max.z, bits(right))
-// link >= 0: internal node index; link < 0: leaf, ~link = position in the Morton-sorted
-// triangle order.  Leaves hold exactly one triangle (sorted_q*[pos], sorted_id[pos]).
-struct LbvhNode {
-    float lo[3];
-    int left;
-    float hi[3];
-    int right;
-};
+// LBVH traversal nodes are defined next to their builder: lbvh.cu (binary: 4 float4 holding both children's boxes and
+// links; 4-ary collapse: 8 float4 per node).
 
 #endif  // PTB_TYPES_H_
