@@ -4,7 +4,10 @@
 // (prog.cl:144-184); here ONE tree over all uploaded triangles is built on the device:
 //
 //   1. k_bounds     centroid box + largest |coordinate| (block reduce + ordered-int atomics)
-//   2. k_morton     63-bit Morton code of the triangle's box centre (21 bits per axis)
+//   2. k_morton     63-bit Morton code of the triangle's box centre (21 bits per axis).  OUTLIERS: a triangle whose box
+//                   spans more than a quarter of the scene (room walls, emitter quads) would inflate every node above
+//                   it; up to LBVH_BIG_MAX of them get the key 2^63, sort behind everything else and stay OUT of the
+//                   tree — the traversal kernels scan that short list once per ray before they enter the tree
 //   3. cub radix sort of (code, upload index) — stable, so equal codes keep upload order
 //   4. k_gather     triangles re-laid in Morton order (3 float4 planes) + their boxes
 //   5. k_hierarchy  Karras 2012 radix tree over the sorted codes (ties split on the index bits)
@@ -96,10 +99,23 @@ __device__ __forceinline__ unsigned long long spread21(unsigned v) {
 }
 
 __global__ void k_morton(const float4 *q0, const float4 *q1, const float4 *q2, int n, const unsigned *bounds,
-                         unsigned long long *keys, int *vals) {
+                         unsigned long long *keys, int *vals, float big_frac, int *n_big) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     Box b = tri_box(q0[i], q1[i], q2[i]);
+    if (big_frac > 0.0f) {
+        float scene = 0.0f, mine = 0.0f;
+        for (int k = 0; k < 3; ++k) {
+            scene = fmaxf(scene, ord2f(bounds[3 + k]) - ord2f(bounds[k]));
+            mine = fmaxf(mine, b.hi[k] - b.lo[k]);
+        }
+        if (mine > big_frac * scene && scene > 0.0f) {
+            keys[i] = 0x8000000000000000ull;
+            vals[i] = i;
+            atomicAdd(n_big, 1);
+            return;
+        }
+    }
     unsigned g[3];
     for (int k = 0; k < 3; ++k) {
         float lo = ord2f(bounds[k]), hi = ord2f(bounds[3 + k]);
@@ -342,8 +358,8 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
     if (!(eps > 0.0f)) eps = 1e-30f;
     b->reach = fmaxf(reach, b->max_abs);
     b->eps = eps;
-    if (b->n_tris >= 2) {
-        int n = b->n_tris;
+    if (b->n_tree >= 2) {
+        int n = b->n_tree;
         k_emit<<<(n - 1 + 255) / 256, 256, 0, st>>>(n, b->leaf_size, eps, (const int2 *)b->range, (const int2 *)b->child,
                                                    b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, b->bvh);
         CK(cudaGetLastError());
@@ -359,11 +375,13 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
 }
 
 int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
-               int n, int leaf_size, cudaStream_t st, char *err, size_t errcap) {
+               int n, int leaf_size, float big_frac, cudaStream_t st, char *err, size_t errcap) {
     lbvh_free(b);
     b->n_tris = n;
+    b->n_tree = n;
+    b->n_big = 0;
     b->leaf_size = leaf_size < 1 ? 1 : (leaf_size > 8 ? 8 : leaf_size);
-    if (n <= 0) { b->root = ~0; b->n_tris = 0; return 0; }
+    if (n <= 0) { b->root = ~0; b->n_tris = 0; b->n_tree = 0; return 0; }
     if (n >= (1 << 28)) { snprintf(err, errcap, "lbvh: too many triangles (%d)", n); return -1; }
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
@@ -382,22 +400,35 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     CK(cudaMemcpyAsync(bounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
     int grid = (n + 255) / 256;
     k_bounds<<<grid > 1184 ? 1184 : grid, 256, 0, st>>>(q0, q1, q2, n, bounds);
-    k_morton<<<grid, 256, 0, st>>>(q0, q1, q2, n, bounds, keys, vals);
+    CK(cudaMemsetAsync(stats, 0, 16, st));
+    k_morton<<<grid, 256, 0, st>>>(q0, q1, q2, n, bounds, keys, vals, big_frac, stats + 2);
     b->launches += 2;
+    int n_big = 0;
+    if (big_frac > 0.0f) {
+        CK(cudaMemcpyAsync(&n_big, stats + 2, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (n_big > LBVH_BIG_MAX || n - n_big < 2) {        // too many outliers (or nothing else): everything goes into the tree
+            k_morton<<<grid, 256, 0, st>>>(q0, q1, q2, n, bounds, keys, vals, 0.0f, stats + 2);
+            b->launches += 1;
+            n_big = 0;
+        }
+    }
+    b->n_big = n_big;
+    b->n_tree = n - n_big;
+    const int m = b->n_tree;                                // triangles under the tree: Morton positions [0, m)
     size_t tmp_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63, st));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
     void *tmp;
     CK(cudaMalloc(&tmp, tmp_bytes + 16));
-    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63, st));
+    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
     k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, vals2, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi);
     CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
     b->launches += 1;
-    CK(cudaMemsetAsync(stats, 0, 16, st));
-    if (n >= 2) {
+    if (m >= 2) {
         CK(cudaMemsetAsync(arrivals, 0, (size_t)n * sizeof(int), st));
-        k_hierarchy<<<grid, 256, 0, st>>>(keys2, n, (int2 *)b->range, (int2 *)b->child, pnode, pleaf);
-        k_refit<<<grid, 256, 0, st>>>(n, (const int2 *)b->child, pnode, pleaf, b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, arrivals);
-        k_depth<<<grid, 256, 0, st>>>(n, b->leaf_size, (const int2 *)b->range, pnode, pleaf, stats, stats + 1);
+        k_hierarchy<<<grid, 256, 0, st>>>(keys2, m, (int2 *)b->range, (int2 *)b->child, pnode, pleaf);
+        k_refit<<<grid, 256, 0, st>>>(m, (const int2 *)b->child, pnode, pleaf, b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, arrivals);
+        k_depth<<<grid, 256, 0, st>>>(m, b->leaf_size, (const int2 *)b->range, pnode, pleaf, stats, stats + 1);
         b->launches += 3;
     }
     unsigned hb[8];
@@ -407,19 +438,19 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     CK(cudaStreamSynchronize(st));
     b->max_abs = ord2f(hb[6]);
     b->max_depth = hs[0];
-    b->n_nodes = n >= 2 ? hs[1] : 0;
-    b->root = (n <= b->leaf_size || n < 2) ? ~(((0) << 3) | (n - 1)) : 0;
+    b->n_nodes = m >= 2 ? hs[1] : 0;
+    b->root = (m <= b->leaf_size || m < 2) ? ~(((0) << 3) | (m - 1)) : 0;
     b->n_nodes4 = 0;
     if (b->root >= 0) {                              // 4-ary collapse: flags, compact ids, node storage
-        k_flag4<<<grid, 256, 0, st>>>(n, b->leaf_size, (const int2 *)b->range, pnode, b->flag4);
-        CK(cudaMemsetAsync(b->flag4 + (n - 1), 0, sizeof(int), st));
+        k_flag4<<<grid, 256, 0, st>>>(m, b->leaf_size, (const int2 *)b->range, pnode, b->flag4);
+        CK(cudaMemsetAsync(b->flag4 + (m - 1), 0, sizeof(int), st));
         size_t scan_bytes = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b->flag4, b->id4, n, st));
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b->flag4, b->id4, m, st));
         void *scan_tmp;
         CK(cudaMalloc(&scan_tmp, scan_bytes + 16));
-        CK(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, b->flag4, b->id4, n, st));
+        CK(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, b->flag4, b->id4, m, st));
         int total = 0;
-        CK(cudaMemcpyAsync(&total, b->id4 + (n - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&total, b->id4 + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         cudaFree(scan_tmp);
         b->launches += 2;
@@ -427,7 +458,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
         CK(dalloc(&b->bvh4, (size_t)8 * (total > 0 ? total : 1)));
     }
     if (lbvh_emit(b, 0.0f, st, err, errcap)) return -1;
-    if (n >= 2 && (size_t)4 * n < ((size_t)1 << 27)) b->bvh_tex = linear_tex(b->bvh, (size_t)4 * n);
+    if (m >= 2 && (size_t)4 * m < ((size_t)1 << 27)) b->bvh_tex = linear_tex(b->bvh, (size_t)4 * m);
     if (b->n_nodes4 > 0 && (size_t)8 * b->n_nodes4 < ((size_t)1 << 27)) b->bvh4_tex = linear_tex(b->bvh4, (size_t)8 * b->n_nodes4);
     CK(cudaEventRecord(e1, st));
     CK(cudaEventSynchronize(e1));

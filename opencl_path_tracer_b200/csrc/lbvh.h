@@ -5,6 +5,8 @@
 #include <stddef.h>
 #include <string.h>
 
+#define LBVH_BIG_MAX 64          // outlier triangles kept out of the tree (lbvh.cu, step 2)
+
 struct Lbvh {
     // traversal data
     float4 *bvh;                  // 4 float4 per node
@@ -20,13 +22,14 @@ struct Lbvh {
     void *range, *child;          // int2 per internal node
     float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
     int n_tris, leaf_size, n_nodes, max_depth;
+    int n_tree, n_big;            // Morton positions [0, n_tree) are under the tree, [n_tree, n_tris) is the outlier list
     float max_abs, reach, eps, build_ms;
     unsigned long long launches;
 };
 
 // q*: staged triangles in upload order (parity layout, holds the vertices); f*: the same triangles in the fast layout
 int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
-               int n, int leaf_size, cudaStream_t st, char *err, size_t errcap);
+               int n, int leaf_size, float big_frac, cudaStream_t st, char *err, size_t errcap);
 // rewrite the traversal nodes with boxes inflated for ray origins up to `reach` from the coordinate origin
 int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap);
 void lbvh_free(Lbvh *b);

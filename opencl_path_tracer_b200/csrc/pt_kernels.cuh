@@ -299,8 +299,24 @@ PT_DEV float safe_rcp(float d) {
     // zero (or denormal) direction components: a huge finite reciprocal keeps (lo-P)*inv free of 0*inf NaNs
     return fabsf(d) > 1e-30f ? 1.0f / d : copysignf(1e30f, d);
 }
+// The outlier triangles the builder kept out of the tree (lbvh.cu step 2: room walls, emitter quads — at most
+// LBVH_BIG_MAX): tested once per ray BEFORE the tree, which also hands the traversal a finite best.t to cull with.
+// Same acceptance and tie rule as a leaf, so closest hit stays the minimum of (t, upload index) over ALL triangles.
+template <bool COUNT>
+PT_DEV void lbvh_big_scan(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &wk) {
+    for (int k = 0; k < sc.big_count; ++k) {
+        const int pos = sc.big_first + k;
+        float t;
+        const bool acc_ = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
+        if (acc_ & (t > 0.0f) & (t <= best.t)) {
+            const int tid = __ldg(sc.sorted_id + pos);
+            if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
+        }
+    }
+}
 template <bool COUNT>
 PT_DEV void lbvh_intersect(const SceneDev &sc, V3 P, V3 D, Closest &best, Work &wk) {
+    lbvh_big_scan<COUNT>(sc, P, D, best, wk);
     const float ix = safe_rcp(D.x), iy = safe_rcp(D.y), iz = safe_rcp(D.z);
     int stack[PT_LBVH_STACK];
     int sp = 0;

@@ -36,6 +36,7 @@ struct SceneDev {
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
+    int big_first, big_count;     // outlier triangles outside the tree: Morton positions [big_first, big_first + big_count)
     // merged scan primitives for the fast brute-force scan (prims.cu); n_prims == 0: not built / nothing merged
     const float4 *pq0, *pq1, *pq2;// fast layout
     const float2 *prim_ab;        // edge slopes (b, a) of the quad's two far edges; (1, 0) for a lone triangle

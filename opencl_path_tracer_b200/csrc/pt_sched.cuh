@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render_sched(const RenderPar
                     ix = safe_rcp(rayD.x); iy = safe_rcp(rayD.y); iz = safe_rcp(rayD.z);
                     ox = rayP.x * ix; oy = rayP.y * iy; oz = rayP.z * iz;
                     best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+                    lbvh_big_scan<COUNT>(sc, rayP, rayD, best, wk);
                     sp = 0;
                     link = sc.bvh_root;
                     st = link >= 0 ? ST_NODE : ST_LEAF;

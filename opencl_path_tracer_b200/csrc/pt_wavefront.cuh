@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
                     ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
                     best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+                    lbvh_big_scan<COUNT>(sc, P, D, best, wk);
                     sp = 0;
                     link = sc.bvh_root;
                     st = link >= 0 ? WF_NODE : WF_LEAF;

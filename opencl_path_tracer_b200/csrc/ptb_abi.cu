@@ -88,6 +88,7 @@ struct State {
     int sum_mode = 0, count_work = 0;
     int lbvh_leaf = 4;
     int merge_prims = 1;
+    float lbvh_big = 0.25f;            // triangles spanning more than this fraction of the scene stay out of the tree (PTB_LBVH_BIG, 0 = off)
     int tex_nodes = 1;                 // node fetches through the texture pipe (PTB_TEX_NODES=0: LSU)
     int wide_bvh = 1;                  // wavefront traversal over the 4-ary collapse of the LBVH (PTB_WIDE_BVH=0: binary)
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
@@ -266,7 +267,7 @@ int ensure_lbvh(float reach) {
     err[0] = 0;
     if (!s.lbvh_valid || s.lbvh_leaf != G.lbvh_leaf) {
         unsigned long long before = s.lbvh.launches;
-        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.n_tris, G.lbvh_leaf, G.stream, err, sizeof err))
+        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.n_tris, G.lbvh_leaf, G.lbvh_big, G.stream, err, sizeof err))
             return fail(PTB_ERR_DEVICE, "%s", err);
         G.launches += s.lbvh.launches - before + 4;   // + the radix-sort passes
         s.lbvh_valid = true;
@@ -333,6 +334,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         p.sc.bvh4 = (G.wide_bvh && s.lbvh.n_nodes4 > 0 && 3 * wide_levels + 1 <= 64) ? s.lbvh.bvh4 : nullptr;
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
+        p.sc.big_first = s.lbvh.n_tree; p.sc.big_count = s.lbvh.n_big;
     }
     p.rnds = (int *)rnds->dptr;
     p.colors = (float4 *)colors->dptr;
@@ -442,6 +444,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_MERGE_PRIMS"))) G.merge_prims = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
     return PTB_SUCCESS;
 }
 

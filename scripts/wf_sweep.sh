@@ -1,8 +1,9 @@
-# experiment driver: wavefront pipeline variants on the 104k-triangle scene (and the 1M grid), Mrays/s
-run() { python bench.py --workload $1 --spp $2 --steps 2 --warmup 3 --pipeline wavefront --no-cpu-baseline --no-e2e 2>&1 | tail -1 | python -c "
+# experiment driver: LBVH scenes (104k spheres at 1080p, 1M grid at 4K), Mrays/s and box/triangle tests per ray
+run() { python bench.py --workload $1 --spp $2 --steps 2 --warmup 3 --pipeline ${3:-wavefront} --no-cpu-baseline --no-e2e 2>&1 | tail -1 | python -c "
 import sys,json
-d=json.loads(sys.stdin.readline()); print(round(d['value']))"; }
-for tex in 0 1; do for wide in 0 1; do
-  echo -n "spheres100k tex=$tex wide=$wide : "; PTB_TEX_NODES=$tex PTB_WIDE_BVH=$wide run spheres100k_1080p_256spp_d4 8
-  echo -n "grid1m tex=$tex wide=$wide : "; PTB_TEX_NODES=$tex PTB_WIDE_BVH=$wide run grid1m_4k_64spp_d4 8
-done; done
+d=json.loads(sys.stdin.readline()); r=d['roofline']; print(round(d['value']), 'B=%.1f T=%.1f' % (r['box_tests_per_ray'], r['tri_tests_per_ray']))"; }
+for big in 0 0.25; do
+  echo -n "spheres100k big=$big wavefront : "; PTB_LBVH_BIG=$big run spheres100k_1080p_256spp_d4 8
+  echo -n "spheres100k big=$big megakernel: "; PTB_LBVH_BIG=$big run spheres100k_1080p_256spp_d4 8 megakernel
+  echo -n "grid1m big=$big wavefront : "; PTB_LBVH_BIG=$big run grid1m_4k_64spp_d4 8
+done
