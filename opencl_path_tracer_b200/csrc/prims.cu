@@ -38,9 +38,9 @@ __device__ void load_tri(const float4 *q0, const float4 *q1, const float4 *q2, i
 struct Quad { int rot; double b, a; };   // rot: index of A's vertex opposite the shared edge
 
 // Can triangle j complete triangle i to a convex planar quad?  (rot < 0: no)
-__device__ Quad match(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int i, int j) {
+__device__ Quad match(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, const int *idx, int i, int j) {
     Quad no = {-1, 1.0, 0.0};
-    if (mati[i] != mati[j]) return no;
+    if (mati[idx ? idx[i] : i] != mati[idx ? idx[j] : j]) return no;
     float4 a[3], b[3];
     D3 Na, Nb;
     load_tri(q0, q1, q2, i, a, Na);
@@ -68,7 +68,7 @@ __device__ Quad match(const float4 *q0, const float4 *q1, const float4 *q2, cons
 }
 
 __device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i, Quad q,
-                     float4 *p0, float4 *p1, float4 *p2, float2 *ab, int *rep, float4 *shade, const uint16_t *mati, int slot) {
+                     float4 *p0, float4 *p1, float4 *p2, float2 *ab, int *rep, float4 *shade, const uint16_t *mati, const int *idx, int slot) {
     float4 a[3];
     D3 N;
     load_tri(q0, q1, q2, i, a, N);
@@ -81,7 +81,7 @@ __device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i
     p1[slot] = make_float4((float)r1.y, (float)r1.z, (float)(mu.x * inv), (float)(mu.y * inv));
     p2[slot] = make_float4((float)(mu.z * inv), (float)(mv.x * inv), (float)(mv.y * inv), (float)(mv.z * inv));
     ab[slot] = make_float2((float)q.b, (float)q.a);
-    rep[slot] = i;
+    rep[slot] = idx ? idx[i] : i;
     // shading record: stored normal + material index, and the tangent frame orthonormal_base (prog.cl:186-204) derives
     // from the UNFLIPPED normal: v2 = (0,-N.z,N.y)/|..| when |N.x|,|N.z| <= 1e-3 else (-N.z,0,N.x)/|..|, v3 = N x v2.
     // (For the flipped normal -N the kernel negates v2 and keeps v3: both are linear/bilinear in N.)
@@ -95,13 +95,13 @@ __device__ void emit(const float4 *q0, const float4 *q1, const float4 *q2, int i
         v2.x = -N.z * rl; v2.y = 0.0; v2.z = N.x * rl;
     }
     const D3 v3 = crossd(N, v2);
-    shade[3 * slot + 0] = make_float4(nx, ny, nz, __int_as_float((int)mati[i]));
+    shade[3 * slot + 0] = make_float4(nx, ny, nz, __int_as_float((int)mati[idx ? idx[i] : i]));
     shade[3 * slot + 1] = make_float4((float)v3.x, (float)v3.y, (float)v3.z, 0.0f);     // X
     shade[3 * slot + 2] = make_float4((float)v2.x, (float)v2.y, (float)v2.z, 0.0f);     // Z
 }
 
 // one block; n <= PRIMS_MAX_TRIS.  Greedy in upload order: triangle i takes the first unpaired j > i that matches.
-__global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int n,
+__global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, const int *idx, int n,
                               float4 *p0, float4 *p1, float4 *p2, float2 *ab, int *rep, float4 *shade, int *n_prims) {
     __shared__ unsigned char used[PRIMS_MAX_TRIS];
     for (int i = threadIdx.x; i < n; i += blockDim.x) used[i] = 0;
@@ -114,12 +114,12 @@ __global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *
             int partner = -1;
             for (int j = i + 1; j < n && partner < 0; ++j) {
                 if (used[j]) continue;
-                const Quad m = match(q0, q1, q2, mati, i, j);
+                const Quad m = match(q0, q1, q2, mati, idx, i, j);
                 if (m.rot >= 0) { partner = j; q = m; }
             }
             used[i] = 1;
             if (partner >= 0) used[partner] = 1;
-            emit(q0, q1, q2, i, q, p0, p1, p2, ab, rep, shade, mati, slot++);
+            emit(q0, q1, q2, i, q, p0, p1, p2, ab, rep, shade, mati, idx, slot++);
         }
         *n_prims = slot;
     }
@@ -127,7 +127,7 @@ __global__ void k_build_prims(const float4 *q0, const float4 *q1, const float4 *
 
 }  // namespace
 
-void prims_build(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, int n, float4 *p0, float4 *p1,
-                 float4 *p2, float2 *ab, int *rep, float4 *shade, int *n_prims_dev, cudaStream_t st) {
-    k_build_prims<<<1, 64, 0, st>>>(q0, q1, q2, mati, n, p0, p1, p2, ab, rep, shade, n_prims_dev);
+void prims_build(const float4 *q0, const float4 *q1, const float4 *q2, const uint16_t *mati, const int *idx, int n, float4 *p0,
+                 float4 *p1, float4 *p2, float2 *ab, int *rep, float4 *shade, int *n_prims_dev, cudaStream_t st) {
+    k_build_prims<<<1, 64, 0, st>>>(q0, q1, q2, mati, idx, n, p0, p1, p2, ab, rep, shade, n_prims_dev);
 }

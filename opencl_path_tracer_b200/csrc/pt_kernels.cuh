@@ -24,6 +24,7 @@
 #include <stdlib.h>
 #include "pt_math.cuh"
 #include "pt_params.h"
+#include "lbvh.h"
 
 namespace PT_NS {
 

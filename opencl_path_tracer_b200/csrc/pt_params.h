@@ -36,6 +36,11 @@ struct SceneDev {
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
+    // the same outliers as merged scan primitives (prims.cu) for the fast flavour; n_big_prims == 0: scan the triangles
+    const float4 *bq0, *bq1, *bq2;
+    const float2 *big_ab;
+    const int *big_rep;           // primitive -> upload index
+    int n_big_prims;
     int big_first, big_count;     // outlier triangles outside the tree: Morton positions [big_first, big_first + big_count)
     // merged scan primitives for the fast brute-force scan (prims.cu); n_prims == 0: not built / nothing merged
     const float4 *pq0, *pq1, *pq2;// fast layout

@@ -177,6 +177,27 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
     __shared__ int2 s_stack[WF_SMEM_STACK * PT_BLOCK];
     int2 *my_stack = s_stack + threadIdx.x;
     int2 deep_stack[PT_LBVH_STACK - WF_SMEM_STACK];
+#if !PT_PARITY
+    // the outlier list as merged primitives in the pair layout of brute_smem_prims (pt_kernels.cuh): at most 32 pairs
+    __shared__ float4 s_big[7 * (LBVH_BIG_MAX / 2)];
+    const int n_big_pairs = COUNT ? 0 : (sc.n_big_prims + 1) >> 1;
+    for (int j = threadIdx.x; j < n_big_pairs; j += PT_BLOCK) {
+        const int ia = 2 * j, ib = 2 * j + 1;
+        const bool hb = ib < sc.n_big_prims;
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const float4 A0 = ldg4(sc.bq0 + ia), A1 = ldg4(sc.bq1 + ia), A2 = ldg4(sc.bq2 + ia);
+        const float4 B0 = hb ? ldg4(sc.bq0 + ib) : z, B1 = hb ? ldg4(sc.bq1 + ib) : z, B2 = hb ? ldg4(sc.bq2 + ib) : z;
+        const float2 sa = __ldg(sc.big_ab + ia), sb = hb ? __ldg(sc.big_ab + ib) : make_float2(1.0f, 0.0f);
+        s_big[7 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
+        s_big[7 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
+        s_big[7 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
+        s_big[7 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
+        s_big[7 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
+        s_big[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
+        s_big[7 * j + 6] = make_float4(-sa.x, -sb.x, -sa.y, -sb.y);
+    }
+    if (n_big_pairs > 0) __syncthreads();
+#endif
     int st = WF_FETCH, link = 0, sp = 0, path = 0;
     bool exhausted = count == 0;
     V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
@@ -214,6 +235,12 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
                     ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
                     best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+#if !PT_PARITY
+                    if (n_big_pairs > 0) {                            // packed scan over the merged outliers, then primitive -> upload index
+                        brute_smem_prims<2>(s_big, n_big_pairs, P, D, best);
+                        if (best.t < PT_NO_HIT) best.tri = __ldg(sc.big_rep + best.tri);
+                    } else
+#endif
                     lbvh_big_scan<COUNT>(sc, P, D, best, wk);
                     sp = 0;
                     link = sc.bvh_root;
@@ -338,7 +365,19 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     int sms = 148, dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    static const int per_sm = getenv("PTB_WF_BLOCKS") ? atoi(getenv("PTB_WF_BLOCKS")) : 9;   // 56 registers, 16 KB stack: 9 fit; measured 1.98 (6) / 2.10 (8) / 2.11 (9) Grays/s
+    // persistent grid: exactly as many blocks as are resident at once (a block that has to wait for a slot would start
+    // after the queue is drained and add a tail); 54-64 registers and 16-20 KB of shared memory give 8-9 per SM
+    static const int want_per_sm = getenv("PTB_WF_BLOCKS") ? atoi(getenv("PTB_WF_BLOCKS")) : 9;
+    const bool wide_ = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+    int occ = 0;
+    if (p.count_work) {
+        if (wide_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, true>, PT_BLOCK, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, PT_BLOCK, 0);
+    } else {
+        if (wide_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, true>, PT_BLOCK, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, PT_BLOCK, 0);
+    }
+    const int per_sm = occ > 0 && occ < want_per_sm ? occ : want_per_sm;
     const int trace_blocks = sms * per_sm;
     const long long max_iters = (long long)p.spp * (p.iterations > 0 ? p.iterations : 0);
     int host_count = n;

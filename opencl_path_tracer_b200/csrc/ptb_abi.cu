@@ -64,6 +64,11 @@ struct Staged {                        // device-internal copy of the scene, val
     int *prim_rep = nullptr, *n_prims_dev = nullptr;
     int n_prims = 0;
     bool prims_valid = false;
+    // the LBVH's outlier list as merged primitives (same records, at most LBVH_BIG_MAX), rebuilt with the tree
+    float4 *b0 = nullptr, *b1 = nullptr, *b2 = nullptr, *big_shade = nullptr;
+    float2 *big_ab = nullptr;
+    int *big_rep = nullptr;
+    int n_big_prims = 0;
 };
 
 struct PendingGen {                    // a deferred gen_ray launch (ptb_set_fuse_gen)
@@ -244,7 +249,7 @@ int ensure_prims() {
         CUDA_OK(cudaMalloc((void **)&s.prim_rep, PRIMS_MAX_TRIS * sizeof(int)));
         CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
     }
-    prims_build(s.q0, s.q1, s.q2, s.mati, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.prim_shade, s.n_prims_dev, G.stream);
+    prims_build(s.q0, s.q1, s.q2, s.mati, nullptr, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.prim_shade, s.n_prims_dev, G.stream);
     CUDA_OK(cudaGetLastError());
     G.launches++;
     int n = 0;
@@ -272,6 +277,27 @@ int ensure_lbvh(float reach) {
         G.launches += s.lbvh.launches - before + 4;   // + the radix-sort passes
         s.lbvh_valid = true;
         s.lbvh_leaf = G.lbvh_leaf;
+        s.n_big_prims = 0;
+        if (s.lbvh.n_big >= 1 && G.merge_prims) {      // the outlier list as merged quads for the fast flavour's packed scan
+            if (!s.b0) {
+                CUDA_OK(cudaMalloc((void **)&s.b0, LBVH_BIG_MAX * sizeof(float4)));
+                CUDA_OK(cudaMalloc((void **)&s.b1, LBVH_BIG_MAX * sizeof(float4)));
+                CUDA_OK(cudaMalloc((void **)&s.b2, LBVH_BIG_MAX * sizeof(float4)));
+                CUDA_OK(cudaMalloc((void **)&s.big_ab, LBVH_BIG_MAX * sizeof(float2)));
+                CUDA_OK(cudaMalloc((void **)&s.big_shade, 3 * LBVH_BIG_MAX * sizeof(float4)));
+                CUDA_OK(cudaMalloc((void **)&s.big_rep, LBVH_BIG_MAX * sizeof(int)));
+            }
+            if (!s.n_prims_dev) CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
+            const int first = s.lbvh.n_tree;
+            prims_build(s.lbvh.sq0 + first, s.lbvh.sq1 + first, s.lbvh.sq2 + first, s.mati, s.lbvh.sorted_id + first, s.lbvh.n_big,
+                        s.b0, s.b1, s.b2, s.big_ab, s.big_rep, s.big_shade, s.n_prims_dev, G.stream);
+            CUDA_OK(cudaGetLastError());
+            G.launches++;
+            int nb = 0;
+            CUDA_OK(cudaMemcpyAsync(&nb, s.n_prims_dev, sizeof nb, cudaMemcpyDeviceToHost, G.stream));
+            CUDA_OK(cudaStreamSynchronize(G.stream));
+            s.n_big_prims = nb > 0 ? nb : 0;
+        }
         if (s.lbvh.max_depth > 62)
             return fail(PTB_ERR_DEVICE, "lbvh: tree depth %d exceeds the traversal stack", s.lbvh.max_depth);
     }
@@ -335,6 +361,9 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
         p.sc.big_first = s.lbvh.n_tree; p.sc.big_count = s.lbvh.n_big;
+        if (fastm && !G.count_work && s.n_big_prims > 0) {
+            p.sc.bq0 = s.b0; p.sc.bq1 = s.b1; p.sc.bq2 = s.b2; p.sc.big_ab = s.big_ab; p.sc.big_rep = s.big_rep; p.sc.n_big_prims = s.n_big_prims;
+        }
     }
     p.rnds = (int *)rnds->dptr;
     p.colors = (float4 *)colors->dptr;
@@ -458,6 +487,7 @@ int ptb_shutdown(void) {
     Staged &s = G.staged;
     cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
     cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_shade); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
+    cudaFree(s.b0); cudaFree(s.b1); cudaFree(s.b2); cudaFree(s.big_ab); cudaFree(s.big_shade); cudaFree(s.big_rep);
     lbvh_free(&s.lbvh);
     s = Staged();
     cudaFree(G.counters);

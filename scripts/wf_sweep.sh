@@ -2,8 +2,7 @@
 run() { python bench.py --workload $1 --spp $2 --steps 2 --warmup 3 --pipeline ${3:-wavefront} --no-cpu-baseline --no-e2e 2>&1 | tail -1 | python -c "
 import sys,json
 d=json.loads(sys.stdin.readline()); r=d['roofline']; print(round(d['value']), 'B=%.1f T=%.1f' % (r['box_tests_per_ray'], r['tri_tests_per_ray']))"; }
-for big in 0 0.25; do
-  echo -n "spheres100k big=$big wavefront : "; PTB_LBVH_BIG=$big run spheres100k_1080p_256spp_d4 8
-  echo -n "spheres100k big=$big megakernel: "; PTB_LBVH_BIG=$big run spheres100k_1080p_256spp_d4 8 megakernel
-  echo -n "grid1m big=$big wavefront : "; PTB_LBVH_BIG=$big run grid1m_4k_64spp_d4 8
+for merge in 0 1; do
+  echo -n "spheres100k merge_prims=$merge : "; PTB_MERGE_PRIMS=$merge run spheres100k_1080p_256spp_d4 8
+  echo -n "grid1m merge_prims=$merge : "; PTB_MERGE_PRIMS=$merge run grid1m_4k_64spp_d4 8
 done
