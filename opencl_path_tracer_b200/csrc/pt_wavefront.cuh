@@ -253,6 +253,21 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
             // ------------------------------------------------------------ NODE steps
 #pragma unroll 1
             for (int k = 0; k < tune.z; ++k) {
+                // pop FIRST: a lane that gets a node link here runs its box tests in this same step
+                if (st == WF_POP) {
+#pragma unroll
+                    for (int attempt = 0; attempt < 2; ++attempt) {
+                        if (st == WF_POP) {
+                            if (sp == 0) {
+                                WF_FINISH();
+                            } else {
+                                --sp;
+                                const int2 e = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK];
+                                if (__int_as_float(e.y) <= best.t) { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
+                            }
+                        }
+                    }
+                }
                 if (WIDE && st == WF_NODE) {
                     // 4-ary node (lbvh.cu): four slab tests, hits sorted by entry distance, nearest visited, rest pushed far-to-near
                     const float4 *nd = sc.bvh4 + 8 * (size_t)link;
@@ -314,20 +329,6 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     link = near_link;
                     st = (hl | hr) ? (near_link >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
                 }
-                if (st == WF_POP) {
-#pragma unroll
-                    for (int attempt = 0; attempt < 2; ++attempt) {
-                        if (st == WF_POP) {
-                            if (sp == 0) {
-                                WF_FINISH();
-                            } else {
-                                --sp;
-                                const int2 e = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK];
-                                if (__int_as_float(e.y) <= best.t) { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
-                            }
-                        }
-                    }
-                }
             }
         } else {
             // ------------------------------------------------------------ LEAF step
@@ -388,7 +389,7 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
         cudaMemsetAsync(p.wf_ctrl + 2, 0, sizeof(int), st);
         const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
         static const int3 tune = make_int3(getenv("PTB_WF_FETCH_MIN") ? atoi(getenv("PTB_WF_FETCH_MIN")) : WF_FETCH_MIN,
-                                           getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 8,
+                                           getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 4,
                                            getenv("PTB_WF_NODE_STEPS") ? atoi(getenv("PTB_WF_NODE_STEPS")) : PT_SCHED_NODE_STEPS);
         if (p.count_work) {
             if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
