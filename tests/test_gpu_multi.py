@@ -1,0 +1,122 @@
+"""Two real GPUs, one process per GPU, NCCL.  Skipped on a single-GPU box; the host-side logic of the same
+code runs world-size 2 over gloo in tests/test_multigpu_cpu.py.
+
+* tile-split: the union of the two ranks' pixel shards after the SUM all-reduce is BITWISE the 1-GPU image (parity
+  flavour, reference seeds).
+* spp-split: rank r renders spp samples of every pixel from seed offset r*W*H into a SUM buffer, one NCCL reduce to rank
+  0, resolve by the total: rank 0's own half is bitwise the 1-GPU render of spp samples, and the merged image agrees
+  with a 1-GPU render of 2*spp samples to Monte-Carlo accuracy (different random numbers: RMSE bound, not equality).
+"""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+W, H, SPP, DEPTH = 256, 192, 16, 4
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _scene(ptb, seed_skip=0):
+    from opencl_path_tracer_b200 import host
+    s = host.Scene(ptb)
+    s.init_Scene(W, H, seed_skip)
+    s.add_Obj(os.path.join(ROOT, "scenes", "cornell.obj"), (555, 0, 0), (1, 1, 1), 0, 0)
+    s.upload_Triangles(); s.upload_Materials()
+    s.iterations = DEPTH
+    cam = host.camera_at(W, H, 39.3, 0, 0, (277.5, 277.5, -800))
+    s._camera = lambda: cam
+    return s
+
+
+def _worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from opencl_path_tracer_b200 import capi, multigpu
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    ptb = capi.Ptb(rank)
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
+    ptb.set_stream(stream.cuda_stream)
+    ptb.set_accel(capi.ACCEL_BRUTE); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+
+    # ---- tile split: reference seeds, my bands of 8 scanlines, SUM all-reduce of disjoint pixel sets
+    group = multigpu.shard_group(W, rows=8)
+    ptb.set_pixel_shard(rank, world, group)
+    s = _scene(ptb)
+    frame = multigpu.DeviceFrame(ptb, W, H, dev)
+    ptb.write(frame.h_rnds, ptb.read(s.buffer_rnds, np.int32, W * H))      # the seeds init_Scene made
+    frame.attach(s)
+    s.render_spp(SPP)
+    ptb.finish()
+    multigpu.merge_tile_split(frame.colors)
+    torch.cuda.synchronize()
+    tile = frame.colors.cpu().numpy().reshape(H, W, 4)
+    ptb.set_pixel_shard(0, 1, 1)
+
+    # ---- spp split: my own seed set, SUM buffer, one reduce to rank 0, resolve by the total
+    ptb.set_accumulate_sum(1)
+    s2 = _scene(ptb, multigpu.rank_seed_skip(rank, W, H))
+    frame2 = multigpu.DeviceFrame(ptb, W, H, dev)
+    ptb.write(frame2.h_rnds, ptb.read(s2.buffer_rnds, np.int32, W * H))
+    frame2.attach(s2)
+    s2.render_spp(SPP)
+    ptb.finish()
+    mine = frame2.colors.cpu().numpy().reshape(H, W, 4).copy()
+    multigpu.reduce_sum_to_root(frame2.colors)
+    torch.cuda.synchronize()
+    if rank == 0:
+        ptb.resolve_sum(frame2.h_colors, SPP * world)
+        ptb.finish()
+    merged = frame2.colors.cpu().numpy().reshape(H, W, 4)
+    ptb.set_accumulate_sum(0)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), tile=tile, mine=mine, merged=merged)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_gpus_tile_split_is_bitwise_and_spp_split_converges(ptb, tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    from opencl_path_tracer_b200 import capi
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (np.load(tmp_path / f"rank{r}.npz") for r in (0, 1))
+
+    def bits(a):
+        return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+    # single-GPU renders in this process
+    ptb.set_accel(capi.ACCEL_BRUTE); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    s = _scene(ptb)
+    s.render_spp(SPP)
+    one = s.download_colors().copy()
+    s.render_spp(SPP)                                      # ... continued to 2*SPP samples
+    two = s.download_colors().copy()
+    ptb.finish()
+    assert (bits(r0["tile"]) == bits(one)).all() and (bits(r1["tile"]) == bits(one)).all()
+    # rank 0's SUM buffer / SPP is the 1-GPU mean up to the rounding of sum-vs-running-mean
+    assert np.abs(r0["mine"][..., :3] / SPP - one[..., :3]).max() <= 2e-5 * max(1.0, float(one[..., :3].max()))
+    # the merged image is a 2*SPP estimate from different random numbers: same expectation, Monte-Carlo distance
+    merged = r0["merged"][..., :3]
+    rel_mean = abs(float(merged.mean()) / float(two[..., :3].mean()) - 1.0)
+    rmse = float(np.sqrt(((merged - two[..., :3]) ** 2).mean()) / two[..., :3].mean())
+    noise = float(np.sqrt(((one[..., :3] - two[..., :3]) ** 2).mean()) / two[..., :3].mean())    # SPP vs 2*SPP of one stream
+    assert rel_mean <= 0.02, rel_mean
+    assert rmse <= 3.0 * noise + 1e-3, (rmse, noise)
