@@ -142,6 +142,11 @@ int ptb_render(int spp);
 /* Restrict the next launches to a pixel subset — the multi-GPU tile split
  * (rank r of n renders interleaved groups of `group` consecutive pixel ids:
  * id/group % n == r).  n==1 restores the full image. */
+/* Closest hit only, for arbitrary rays: `rays` holds n_rays Ray records (32 B, prog.cl:7-9), `out` receives n_rays pairs
+ * {float t; int triangle} with the scene currently bound to trace_ray's arguments, the selected structure
+ * (ptb_set_accel), flavour and pipeline — first_intersect / kd_intersect semantics (prog.cl:113-184): smallest t > 0, ties
+ * to the lowest upload index; (-1, -1) on a miss.  Blocking.  The test surface for "every structure == brute force". */
+int ptb_closest_hit(ptb_mem rays, size_t n_rays, ptb_mem out);
 int ptb_set_pixel_shard(int rank, int nranks, int group);
 /* spp-split support: accumulate plain per-pixel sums (not the running mean) so
  * ranks can be added: colors[id] += sample; combine with ptb_resolve_sum. */

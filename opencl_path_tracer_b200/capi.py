@@ -21,7 +21,7 @@ SYMBOLS = [
     "ptb_set_fuse_gen", "ptb_set_lbvh_leaf", "ptb_set_merge_prims", "ptb_scan_prims", "ptb_get_accel", "ptb_build_accel", "ptb_render",
     "ptb_set_pixel_shard", "ptb_set_accumulate_sum", "ptb_resolve_sum", "ptb_set_count_work", "ptb_get_counters",
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
-    "ptb_accel_stats", "ptb_launch_count",
+    "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit",
 ]
 
 
@@ -53,7 +53,7 @@ def load_library(path=None):
         "ptb_init": (i, [i]), "ptb_shutdown": (i, []), "ptb_device_string": (i, [i, cp, sz]),
         "ptb_device_compute_units": (i, []), "ptb_backend_name": (cp, []),
         "ptb_alloc": (u64, [sz]), "ptb_alloc_image": (u64, [i, i]), "ptb_retain": (i, [u64]), "ptb_release": (i, [u64]),
-        "ptb_write": (i, [u64, sz, sz, vp]), "ptb_read": (i, [u64, sz, sz, vp]), "ptb_mem_size": (sz, [u64]),
+        "ptb_write": (i, [u64, sz, sz, vp]), "ptb_read": (i, [u64, sz, sz, vp]), "ptb_mem_size": (sz, [u64]), "ptb_closest_hit": (i, [u64, sz, u64]),
         "ptb_ingest_mesh": (i, [u64, sz, vp, sz, vp, vp, sz, vp, vp, C.c_float, C.c_float, i]),
         "ptb_wrap_device": (u64, [vp, sz]), "ptb_device_ptr": (vp, [u64]),
         "ptb_kernel_id": (i, [cp]), "ptb_set_arg": (i, [i, i, sz, vp]), "ptb_set_arg_mem": (i, [i, i, u64]),
@@ -147,6 +147,21 @@ class Ptb:
         self._ck(self.lib.ptb_ingest_mesh(h, first_tri, v.ctypes.data, len(v), f.ctypes.data, m.ctypes.data, len(f),
                                           ps.ctypes.data, sc.ctypes.data, float(pitch), float(yaw), int(mat_offset)),
                  "ptb_ingest_mesh")
+
+    def closest_hit(self, origins, dirs):
+        """ptb_closest_hit on (n,3) origins / directions: returns (t float32[n], triangle int32[n]); (-1, -1) = miss."""
+        o = np.ascontiguousarray(origins, dtype=np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, dtype=np.float32).reshape(-1, 3)
+        n = len(o)
+        rays = np.zeros((n, 8), dtype=np.float32)
+        rays[:, 0:3], rays[:, 4:7] = o, d
+        h_rays, h_out = self.upload(rays), self.alloc(max(n, 1) * 8)
+        try:
+            self._ck(self.lib.ptb_closest_hit(h_rays, n, h_out), "ptb_closest_hit")
+            raw = self.read(h_out, np.float32, 2 * n).reshape(n, 2)
+        finally:
+            self.release(h_rays); self.release(h_out)
+        return raw[:, 0].copy(), raw[:, 1].copy().view(np.int32)
 
     def upload(self, array):
         a = np.ascontiguousarray(array)

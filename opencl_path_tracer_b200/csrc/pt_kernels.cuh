@@ -678,6 +678,42 @@ __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n)
     r[1] = make_float4(D.x, D.y, D.z, 0.0f);
 }
 
+// ---------------------------------------------------------------- closest hit only (ptb_closest_hit)
+// One thread per ray through the same closest-hit code the path kernels call: the test surface for
+// "LBVH == brute force on arbitrary rays, ties included" (SURVEY §7 step 5).  out = (t, bits(triangle)), (-1, -1) on a miss.
+template <int ACCEL>
+__global__ void __launch_bounds__(128) k_closest_hit(const RenderParams p, const RefRay *rays, size_t n, float2 *out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 *r = reinterpret_cast<const float4 *>(rays + i);
+    const V3 P = v3(r[0]), D = v3(r[1]);
+    Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    if (ACCEL == PT_ACCEL_BRUTE) brute_global<false>(p.sc, 0, p.sc.n_tris, P, D, best, wk);
+    else if (ACCEL == PT_ACCEL_REFBVH) refbvh_intersect<false>(p.sc, P, D, best, wk);
+    else lbvh_intersect<false>(p.sc, P, D, best, wk);
+    const bool hit = best.t < PT_NO_HIT;
+    out[i] = make_float2(hit ? best.t : -1.0f, __int_as_float(hit ? best.tri : -1));
+}
+// the wavefront trace kernel on an arbitrary ray list: rays -> its ray records + an identity queue, and back
+__global__ void k_ch_pack(const RefRay *rays, size_t n, float4 *ray0, float4 *ray1, int *queue, int *ctrl) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { ctrl[0] = (int)n; ctrl[1] = 0; ctrl[2] = 0; ctrl[3] = 0; }
+    if (i >= n) return;
+    const float4 *r = reinterpret_cast<const float4 *>(rays + i);
+    const float4 a = r[0], b = r[1];
+    ray0[i] = make_float4(a.x, a.y, a.z, b.x);
+    ray1[i] = make_float4(b.y, b.z, PT_NO_HIT, __int_as_float(0x7fffffff));
+    queue[i] = (int)i;
+}
+__global__ void k_ch_unpack(const float4 *ray1, size_t n, float2 *out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 b = ray1[i];
+    const bool hit = b.z < PT_NO_HIT;
+    out[i] = make_float2(hit ? b.z : -1.0f, hit ? b.w : __int_as_float(-1));
+}
+
 // ---------------------------------------------------------------- host-side dispatch
 template <int ACCEL, bool COUNT, int SMEM, int MINB = 1, int U = 2, bool NONNEG = false>
 static void launch_one(const RenderParams &p, cudaStream_t st) {
@@ -723,6 +759,34 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
         else if (sched == 3) k_render_sched<false, 8><<<grid, PT_BLOCK, 0, st>>>(p);
         else k_render_sched<false, 1><<<grid, PT_BLOCK, 0, st>>>(p);
     }
+}
+
+// scratch (wavefront only): n * 36 + 16 bytes
+int launch_closest_hit(const RenderParams &p0, const RefRay *rays, size_t n, float2 *out, bool wavefront, void *scratch, cudaStream_t st) {
+    if (n == 0) return 0;
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    if (wavefront && p0.accel == PT_ACCEL_LBVH && scratch) {
+        RenderParams p = p0;
+        char *b = (char *)scratch;
+        p.wf_ray0 = (float4 *)b; b += n * 16;
+        p.wf_ray1 = (float4 *)b; b += n * 16;
+        p.wf_queue[0] = (int *)b; b += n * 4;
+        p.wf_ctrl = (int *)b;
+        k_ch_pack<<<blocks, 128, 0, st>>>(rays, n, p.wf_ray0, p.wf_ray1, p.wf_queue[0], p.wf_ctrl);
+        int sms = 148, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+        const int3 tune = make_int3(WF_FETCH_MIN, 4, PT_SCHED_NODE_STEPS);
+        if (wide) k_wf_trace<false, true><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
+        else k_wf_trace<false, false><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
+        k_ch_unpack<<<blocks, 128, 0, st>>>(p.wf_ray1, n, out);
+        return 3;
+    }
+    if (p0.accel == PT_ACCEL_BRUTE) k_closest_hit<PT_ACCEL_BRUTE><<<blocks, 128, 0, st>>>(p0, rays, n, out);
+    else if (p0.accel == PT_ACCEL_REFBVH) k_closest_hit<PT_ACCEL_REFBVH><<<blocks, 128, 0, st>>>(p0, rays, n, out);
+    else k_closest_hit<PT_ACCEL_LBVH><<<blocks, 128, 0, st>>>(p0, rays, n, out);
+    return 1;
 }
 
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t st) {

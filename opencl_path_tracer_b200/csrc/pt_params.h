@@ -99,11 +99,13 @@ namespace pt_parity {
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
 int launch_wavefront(const RenderParams &p, cudaStream_t s);   // returns the number of kernels launched
+int launch_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, bool wavefront, void *scratch, cudaStream_t s);
 }
 namespace pt_fast {
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
 int launch_wavefront(const RenderParams &p, cudaStream_t s);
+int launch_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, bool wavefront, void *scratch, cudaStream_t s);
 }
 
 #endif  // PT_PARAMS_H_

@@ -806,6 +806,36 @@ int ptb_render(int spp) {
     return run_render(p);
 }
 
+int ptb_closest_hit(ptb_mem rays_h, size_t n_rays, ptb_mem out_h) {
+    NEED_INIT();
+    MemObj *rays = find(rays_h), *out = find(out_h);
+    if (!rays || !out) return fail(PTB_ERR_INVALID_MEM, "ptb_closest_hit: bad handle");
+    if (rays->bytes < n_rays * sizeof(RefRay) || out->bytes < n_rays * 8)
+        return fail(PTB_ERR_INVALID_VALUE, "ptb_closest_hit: %zu rays need %zu + %zu bytes", n_rays, n_rays * sizeof(RefRay), n_rays * 8);
+    if (n_rays == 0) return PTB_SUCCESS;
+    int rc = flush_pending();
+    if (rc) return rc;
+    bool ok = true;
+    RefCamera cam = arg_val<RefCamera>(PTB_KERNEL_TRACE_RAY, 11, &ok);
+    if (!ok) return fail(PTB_ERR_INVALID_ARGS, "ptb_closest_hit: bind the scene through trace_ray's arguments first (argument 11 is not set)");
+    RenderParams p;
+    rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, 1, false);
+    if (rc) return rc;
+    const bool wf = G.pipe != PTB_PIPE_MEGAKERNEL && p.accel == PT_ACCEL_LBVH;
+    void *scratch = nullptr;
+    if (wf) CUDA_OK(cudaMalloc(&scratch, n_rays * 36 + 64));
+    const int k = G.math == PTB_MATH_PARITY
+                      ? pt_parity::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, G.stream)
+                      : pt_fast::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, G.stream);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    cudaFree(scratch);
+    if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_closest_hit: %s", cudaGetErrorString(e));
+    G.launches += (unsigned long long)k;
+    out->version++;
+    return PTB_SUCCESS;
+}
+
 int ptb_set_pixel_shard(int rank, int n, int group) {
     if (n < 1 || rank < 0 || rank >= n || group < 1) return PTB_ERR_INVALID_VALUE;
     int rc = G.inited ? flush_pending() : PTB_SUCCESS;
