@@ -377,7 +377,8 @@ def main():
                        "scan_primitives": int(ptb.scan_prims()) if accel_used.startswith("brute") and args.math == "fast" else None,
                        "accel": accel_used, "math": args.math, "pipeline": args.pipeline,
                        "parallelism": "single GPU" if world == 1 else f"spp-split x{world} + NCCL reduce(SUM) of the accumulation buffer per step",
-                       "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s},
+                       "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s,
+                       "lbvh": ptb.accel_stats() if accel_used == "lbvh" else None},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "bit_exact_flavour": exact,
         }
         EMIT(json.dumps(line))
