@@ -127,6 +127,10 @@ int ptb_set_lbvh_leaf(int max_tris); /* 1..8 triangles per LBVH leaf (default 4)
 /* Fast flavour, brute-force scan only: merge coplanar same-material triangle pairs that form a convex quad
  * (a fan-triangulated quad, main.cpp:558) into one scan primitive (default 1).  Never used by PTB_MATH_PARITY. */
 int ptb_set_merge_prims(int on);
+/* Parity flavour, shared-memory brute-force scan only: put a conservative pre-filter (the fast flavour's packed test with
+ * a rigorous error margin) in front of prog.cl:94-112's exact test, which then runs only on the triangles the filter
+ * cannot rule out (default 1).  The result is bit-identical either way; 0 evaluates the exact test on every triangle. */
+int ptb_set_parity_filter(int on);
 int ptb_scan_prims(void);      /* primitives the last fast brute-force launch scanned (== triangle count when nothing merged) */
 int ptb_get_accel(void);       /* the structure the next launch will really use (AUTO resolved)         */
 int ptb_build_accel(void);     /* force the (lazy) staging + LBVH build now; returns when done          */

@@ -163,7 +163,6 @@ PT_DEV void brute_global(const SceneDev &sc, int from, int to, V3 P, V3 V, Close
     }
 }
 
-#if !PT_PARITY
 // ---- Blackwell packed-FP32 scan: two triangles per step with FFMA2 / FADD2 / FMUL2 (sm_100 f32x2)
 // The brute-force scan is issue-bound (86 % issue-slot utilisation, profiles/r01_render_v3.txt), so
 // the fix is fewer instructions: lane .x of every float2 carries triangle 2j, lane .y triangle 2j+1,
@@ -184,6 +183,7 @@ PT_DEV RayPair ray_pair(V3 P, V3 V) {
 PT_DEV float2 dot2(float2 ax, float2 ay, float2 az, float2 bx, float2 by, float2 bz) {
     return __ffma2_rn(az, bz, __ffma2_rn(ay, by, __fmul2_rn(ax, bx)));
 }
+#if !PT_PARITY
 template <int U>
 PT_DEV void brute_smem_pairs(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Closest &best) {
     const RayPair r = ray_pair(P, V);
@@ -232,6 +232,94 @@ PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Clo
         const float2 w = __ffma2_rn(u, make_float2(L6.z, L6.w), __ffma2_rn(v, neg1, one));     // 1 - v - a*u
         closest_update(best, fminf(fminf(u.x, v.x), fminf(q.x, w.x)) >= 0.0f, t.x, 2 * j);
         closest_update(best, fminf(fminf(u.y, v.y), fminf(q.y, w.y)) >= 0.0f, t.y, 2 * j + 1);
+    }
+}
+#endif
+
+#if PT_PARITY
+// ---- Parity flavour: conservative pre-filter in front of the exact test
+// The exact test (tri_accept above: true divisions, three cross products, ~100 instructions) decides every hit, so the
+// image stays bit-identical to prog.cl; the filter only removes triangles the exact test is CERTAIN to reject, at the
+// packed-FP32 cost of the fast flavour's test.  With e1 = r2-r1, e2 = r3-r1, den = N.(e1 x e2) and the decomposition
+// p - r1 = u e1 + v e2 + h N, prog.cl's three edge expressions are, in exact arithmetic,
+//     edge1 = v den,   edge2 = (1-u-v) den,   edge3 = u den                 (N.(e x N) = 0 kills the h term)
+// and the fast layout's (mu, mv) produce exactly this u, v.  In float arithmetic (unit roundoff eps = 2^-24):
+//   * an edge expression that prog.cl computes as >= 0 is >= -16 eps |e_k| |p - v_k| exactly, i.e. its barycentric
+//     coordinate is >= -16 eps L (|p - r1| + L) / den, L = the longest edge;
+//   * the filter's t' and prog.cl's t both approximate N.(r1-P)/N.V; their difference is below
+//     eps (|r1-P| + |t|) (19/|b| + 6) with b = N.V, as long as |b| is not within rounding of 0;
+//   * a barycentric coordinate changes by at most L/den per unit of distance, the roundings of P + V t and of the
+//     filter's own dot products add about 8 eps (|P| + |t| + |r1-P|) L / den.
+// Summing: |filter coordinate - reference coordinate| < eps (L/den) D (40 + 19/|b|) with D = 2|P|_1 + 2(L + |r1|_1) + |t'|
+// (an upper bound of every length above).  The filter rejects only when
+//     min(u', v', 1-u'-v') < -delta,  delta = 64 eps (L/den) D g,   g = 2 + 1/|b'| + 2^-11/|b'|^2     (> 3x the bound)
+//     or t' < -dt,                    dt    = 64 eps D g                                              (prog.cl: t < 0 misses)
+// The quadratic term makes grazing rays (|b'| < 2^-17, where b' is rounding noise) candidates unconditionally:
+// g >= 2^23 there, so delta >= 32 D L/den > |any coordinate| and dt >= 32 D > |t'|.  NaN or inf anywhere compares
+// false and the triangle stays a candidate; a record whose den is not positive (normal against the winding, or a
+// degenerate triangle) gets c = inf and is always a candidate.  Survivors take the exact test in upload order, so ties
+// still go to the lower index (prog.cl:118).
+// Shared memory per 32 triangles: 16 pair records of 7 float4 — the six of brute_smem_pairs and (c.A c.B Lt.A Lt.B),
+// c = 2^-18 L/den, Lt = 2 (L + |r1|_1).
+#define PT_FILTER_MAX_TRIS 1024
+PT_DEV void filter_record(float4 r1n, float4 r2n, float4 r3n, float &c, float &Lt) {
+    const V3 r1 = v3(r1n), r2 = v3(r2n), r3 = v3(r3n), N = v3(r1n.w, r2n.w, r3n.w);
+    const V3 e1 = r2 - r1, e2 = r3 - r1, e3 = r3 - r2;
+    const float L = sqrtf(fmaxf(fmaxf(dot(e1, e1), dot(e2, e2)), dot(e3, e3))) * 1.0001f;
+    const float den = dot(N, cross(e1, e2));
+    c = den > 0.0f ? 3.8147e-6f * (L / den) * 1.0001f : PT_NO_HIT;        // 2^-18 = 3.8146973e-6, rounded up
+    Lt = 2.0f * (L + (fabsf(r1.x) + fabsf(r1.y) + fabsf(r1.z)));
+}
+PT_DEV void brute_smem_filtered(const float4 *s_exact, const float4 *s_filt, int n, V3 P, V3 V, Closest &best, Work &wk) {
+    const RayPair r = ray_pair(P, V);
+    const float Pn = 2.0f * (fabsf(P.x) + fabsf(P.y) + fabsf(P.z));
+    const float2 Pn2 = make_float2(Pn, Pn), one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
+    const float2 two = make_float2(2.0f, 2.0f), q11 = make_float2(4.8828125e-4f, 4.8828125e-4f);   // 2^-11
+    for (int base = 0; base < n; base += 32) {
+        unsigned mask = 0;
+        const float4 *f = s_filt + 7 * (base >> 1);
+#pragma unroll 1
+        for (int jj = 0; jj < 16; jj += 4) {
+        unsigned m8 = 0;
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+            const int j = jj + k4;
+            const float4 L0 = f[7 * j], L1 = f[7 * j + 1], L2 = f[7 * j + 2], L3 = f[7 * j + 3];
+            const float4 L4 = f[7 * j + 4], L5 = f[7 * j + 5], L6 = f[7 * j + 6];
+            const float2 Nx = make_float2(L0.x, L0.y), Ny = make_float2(L0.z, L0.w), Nz = make_float2(L1.x, L1.y);
+            const float2 wx = __fadd2_rn(make_float2(L1.z, L1.w), r.Px);
+            const float2 wy = __fadd2_rn(make_float2(L2.x, L2.y), r.Py);
+            const float2 wz = __fadd2_rn(make_float2(L2.z, L2.w), r.Pz);
+            const float2 a = dot2(Nx, Ny, Nz, wx, wy, wz);
+            const float2 b = dot2(Nx, Ny, Nz, r.nVx, r.nVy, r.nVz);
+            const float2 inv = make_float2(pt_rcp_approx(b.x), pt_rcp_approx(b.y));
+            const float2 t = __fmul2_rn(a, inv);
+            const float2 px = __ffma2_rn(r.Vx, t, wx), py = __ffma2_rn(r.Vy, t, wy), pz = __ffma2_rn(r.Vz, t, wz);
+            const float2 u = dot2(make_float2(L3.x, L3.y), make_float2(L3.z, L3.w), make_float2(L4.x, L4.y), px, py, pz);
+            const float2 v = dot2(make_float2(L4.z, L4.w), make_float2(L5.x, L5.y), make_float2(L5.z, L5.w), px, py, pz);
+            const float2 q = __ffma2_rn(__fadd2_rn(u, v), neg1, one);
+            const float2 ai = make_float2(fabsf(inv.x), fabsf(inv.y));
+            const float2 g = __ffma2_rn(__ffma2_rn(ai, q11, one), ai, two);                 // 2 + ai + 2^-11 ai^2
+            const float2 D = __fadd2_rn(__fadd2_rn(Pn2, make_float2(L6.z, L6.w)), make_float2(fabsf(t.x), fabsf(t.y)));
+            const float2 dg = __fmul2_rn(D, g);
+            const float2 delta = __fmul2_rn(make_float2(L6.x, L6.y), dg);
+            const float2 dt = __fmul2_rn(make_float2(3.8147e-6f, 3.8147e-6f), dg);
+            const bool rej_a = (fminf(fminf(u.x, v.x), q.x) < -delta.x) | (t.x < -dt.x);
+            const bool rej_b = (fminf(fminf(u.y, v.y), q.y) < -delta.y) | (t.y < -dt.y);
+            m8 |= rej_a ? 0u : 1u << (2 * k4);
+            m8 |= rej_b ? 0u : 2u << (2 * k4);
+        }
+        mask |= m8 << (2 * jj);
+        }
+        const int left = n - base;
+        if (left < 32) mask &= (1u << left) - 1u;
+        while (mask) {                                           // the exact test of prog.cl on the survivors, in upload order
+            const int i = base + __ffs(mask) - 1;
+            mask &= mask - 1;
+            float t;
+            const bool acc = tri_accept<false>(s_exact[3 * i], s_exact[3 * i + 1], s_exact[3 * i + 2], P, V, t, wk);
+            closest_update(best, acc, t, i);
+        }
     }
 }
 #endif
@@ -514,6 +602,34 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
         }
         __syncthreads();
     }
+#if PT_PARITY
+    const int n_filt = ((sc.n_tris + 31) >> 5) * 16 * 7;          // float4 of filter records (whole 32-triangle chunks)
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 4) {      // filter records, then the exact records (brute_smem_filtered)
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (int j = threadIdx.x; j < n_filt / 7; j += PT_BLOCK) {
+            const int ia = 2 * j, ib = 2 * j + 1;
+            const bool ha = ia < sc.n_tris, hb = ib < sc.n_tris;      // padding pairs are masked off by the scan
+            const float4 A0 = ha ? ldg4(sc.fq0 + ia) : z, A1 = ha ? ldg4(sc.fq1 + ia) : z, A2 = ha ? ldg4(sc.fq2 + ia) : z;
+            const float4 B0 = hb ? ldg4(sc.fq0 + ib) : z, B1 = hb ? ldg4(sc.fq1 + ib) : z, B2 = hb ? ldg4(sc.fq2 + ib) : z;
+            float ca = PT_NO_HIT, cb = PT_NO_HIT, la = 0.0f, lb = 0.0f;
+            if (ha) filter_record(ldg4(sc.q0 + ia), ldg4(sc.q1 + ia), ldg4(sc.q2 + ia), ca, la);
+            if (hb) filter_record(ldg4(sc.q0 + ib), ldg4(sc.q1 + ib), ldg4(sc.q2 + ib), cb, lb);
+            s_tris[7 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
+            s_tris[7 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
+            s_tris[7 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
+            s_tris[7 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
+            s_tris[7 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
+            s_tris[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
+            s_tris[7 * j + 6] = make_float4(ca, cb, la, lb);
+        }
+        for (int i = threadIdx.x; i < sc.n_tris; i += PT_BLOCK) {
+            s_tris[n_filt + 3 * i] = ldg4(sc.q0 + i);
+            s_tris[n_filt + 3 * i + 1] = ldg4(sc.q1 + i);
+            s_tris[n_filt + 3 * i + 2] = ldg4(sc.q2 + i);
+        }
+        __syncthreads();
+    }
+#endif
 #if !PT_PARITY
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) {      // pair layout for the packed-FP32 scan
         const int n_pairs = (sc.n_tris + 1) >> 1;
@@ -601,6 +717,9 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
             if (SMEM == 3) {
                 brute_smem_prims<U>(s_tris, n_prim_pairs, rayP, rayD, best);     // best.tri = primitive index
             } else
+#endif
+#if PT_PARITY
+            if (SMEM == 4) brute_smem_filtered(s_tris + n_filt, s_tris, sc.n_tris, rayP, rayD, best, wk); else
 #endif
             if (SMEM == 1) brute_smem<COUNT>(s_tris, sc.n_tris, rayP, rayD, best, wk);
             else brute_global<COUNT>(sc, 0, sc.n_tris, rayP, rayD, best, wk);
@@ -722,6 +841,7 @@ static void launch_one(const RenderParams &p, cudaStream_t st) {
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 1) smem = (size_t)p.sc.n_tris * 3 * sizeof(float4);
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 2) smem = (size_t)((p.sc.n_tris + 1) / 2) * 6 * sizeof(float4);
     if (ACCEL == PT_ACCEL_BRUTE && SMEM == 3) smem = ((size_t)((p.sc.n_prims + 1) / 2) * 7 + 3 * (size_t)p.sc.n_prims) * sizeof(float4);
+    if (ACCEL == PT_ACCEL_BRUTE && SMEM == 4) smem = ((size_t)((p.sc.n_tris + 31) / 32) * 16 * 7 + 3 * (size_t)p.sc.n_tris) * sizeof(float4);
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(k_render<ACCEL, COUNT, SMEM, MINB, U, NONNEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_render<ACCEL, COUNT, SMEM, MINB, U, NONNEG><<<grid, PT_BLOCK, smem, st>>>(p);
@@ -743,6 +863,7 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
             else launch_one<PT_ACCEL_BRUTE, false, 2, 8, 4>(p, st);   // packed-FP32 pair scan; 64 registers -> 8 blocks/SM, 4 pairs in flight
                                                                       // (measured best of 8 (occupancy, unroll) variants: 23.0 vs 20.7 Grays/s)
 #else
+            else if (p.parity_filter && p.sc.n_tris <= PT_FILTER_MAX_TRIS) launch_one<PT_ACCEL_BRUTE, false, 4, 4>(p, st);
             else launch_one<PT_ACCEL_BRUTE, false, 1>(p, st);
 #endif
         } else {

@@ -64,9 +64,10 @@ PT_DEV float pt_pow(float a, float b) {
     return exp2f(b * __log2f(a));
 }
 PT_DEV void pt_disk_angle(float rnd2, float &c, float &s) { sincospif(2.0f * rnd2, &s, &c); }
-// one MUFU.RCP, no denormal rescue (a plane-distance denominator that small means a grazing ray: t overflows either way)
-PT_DEV float pt_rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 #endif
+// one MUFU.RCP, no denormal rescue (a plane-distance denominator that small means a grazing ray: t overflows either way).
+// The parity flavour uses it only inside its conservative pre-filter, never in a value that reaches the image.
+PT_DEV float pt_rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 // OpenCL fmin/fmax/max on floats (NaN -> the other operand for fmin/fmax; prog.cl uses fmax on scalars)
 PT_DEV float pt_fmax(float a, float b) { return fmaxf(a, b); }

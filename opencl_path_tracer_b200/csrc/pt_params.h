@@ -21,6 +21,7 @@ struct SceneDev {
     // staged triangles in upload order, 3 float4 planes in the layout of the arithmetic flavour that
     // reads them (parity: vertices + normal; fast: normal, anchor, barycentric gradients — pt_kernels.cuh)
     const float4 *q0, *q1, *q2;
+    const float4 *fq0, *fq1, *fq2;// always the fast layout (the parity flavour's conservative pre-filter reads it)
     const uint16_t *mati;
     int n_tris;
     const RefMaterial *mats;      // as uploaded (prog.cl:1-5)
@@ -69,6 +70,7 @@ struct RenderParams {
     int sum_mode;                 // 1: colors += sample (spp-split), 0: running mean (prog.cl:379)
     int accel;                    // PT_ACCEL_*
     int count_work;               // 1: also count box / triangle tests
+    int parity_filter;            // parity flavour, brute force: conservative FFMA2 pre-filter in front of the exact test (pt_kernels.cuh)
     int rng_nonneg;               // 1: every RNG state of this launch was verified to lie in [0, 2^31) (pt_rand_nonneg)
     unsigned long long *counters; // PT_CNT_WORDS words
     // wavefront pipeline scratch (pt_wavefront.cuh), one path per pixel, allocated by ptb_abi.cu; null = megakernel only

@@ -148,3 +148,46 @@ def test_fast_flavour_on_the_same_edge_scenes(ptb):
             assert st["frac_rel_le_1e-4"] >= 0.995 and st["rmse_over_mean"] <= 0.02, st
         else:
             assert (got[..., :3] == 0).all() and (rnds == wrnds).all()
+
+
+def soup(seed, n):
+    """a hostile triangle soup around the open box: needles (aspect 1e4), specks, slivers through the camera position,
+    triangles in planes that contain the eye (N.V ~ 0 for whole fans of rays) and far-away giants"""
+    rng = np.random.default_rng(seed)
+    t = open_box()
+    eye = np.array([0.0, 90.0, -300.0])
+    for k in range(n):
+        kind = k % 6
+        c = rng.uniform([-90, 10, -80], [90, 190, 90])
+        if kind == 0:                                  # needle
+            d = rng.normal(size=3); d /= np.linalg.norm(d)
+            e = np.cross(d, rng.normal(size=3)); e /= np.linalg.norm(e)
+            a, b, cc = c, c + 80 * d, c + 80 * d + 0.008 * e
+        elif kind == 1:                                # speck
+            a, b, cc = c, c + rng.normal(size=3) * 1e-3, c + rng.normal(size=3) * 1e-3
+        elif kind == 2:                                # plane through the eye: every ray towards it grazes
+            a, b, cc = eye + (c - eye) * 0.5, eye + (c - eye) * 1.5, eye + (c - eye) * 1.0 + rng.normal(size=3) * 20
+        elif kind == 3:                                # giant, far away
+            a, b, cc = c * 40 + 3000, c * 40 + 3000 + rng.normal(size=3) * 4000, c * 40 + 3000 + rng.normal(size=3) * 4000
+        elif kind == 4:                                # ordinary
+            a, b, cc = c, c + rng.normal(size=3) * 30, c + rng.normal(size=3) * 30
+        else:                                          # sliver sharing an edge with the previous triangle
+            a, b, cc = np.array(t[-1][0]), np.array(t[-1][1]), np.array(t[-1][1]) + rng.normal(size=3) * 1e-2
+        t.append((tuple(map(float, a)), tuple(map(float, b)), tuple(map(float, cc)), int(rng.integers(0, 5))))
+    return t
+
+
+@pytest.mark.parametrize("seed,n", [(1, 40), (2, 120), (3, 300)])
+def test_parity_prefilter_on_a_hostile_soup(ptb, seed, n):
+    """the pre-filter of the parity brute-force scan must never drop a triangle the exact test accepts: oracle, filter on
+    and filter off agree bit for bit on needles, specks, grazing planes and far giants"""
+    surf = build(soup(seed, n), 96, 64, 5)
+    try:
+        ptb.set_parity_filter(1)
+        on, rnds_on, want, wrnds = both(ptb, surf, 6, capi.ACCEL_BRUTE)
+        ptb.set_parity_filter(0)
+        off, rnds_off, _, _ = both(ptb, surf, 6, capi.ACCEL_BRUTE)
+    finally:
+        ptb.set_parity_filter(1)
+    assert same_bits(on, off) and (rnds_on == rnds_off).all()
+    assert same_bits(on, want) and (rnds_on == wrnds).all()

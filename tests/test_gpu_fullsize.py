@@ -86,6 +86,20 @@ def test_c2_closest_hit_structure_and_pipeline_do_not_change_a_bit(ptb, c2_parit
     assert (bits(colors) == bits(c2_parity_64[0])).all() and (rnds == c2_parity_64[1]).all()
 
 
+def test_c2_parity_prefilter_does_not_change_a_bit(ptb, c2_parity_64):
+    """the parity flavour's conservative pre-filter (on by default, so c2_parity_64 used it) against the exact test on
+    every triangle: ~50 M rays, identical bits and RNG states"""
+    try:
+        ptb.set_parity_filter(0)
+        s = cornell(ptb, capi.ACCEL_BRUTE, capi.MATH_PARITY)
+        s.render_spp(64)
+        colors, rnds = s.download_colors(), s.download_rnds()
+        release(s)
+    finally:
+        ptb.set_parity_filter(1)
+    assert (bits(colors) == bits(c2_parity_64[0])).all() and (rnds == c2_parity_64[1]).all()
+
+
 def test_c2_pixel_shards_tile_the_frame_bitwise(ptb, c2_parity_64):
     n, group = 4, 8 * W
     total = np.zeros((H, W, 4), dtype=np.float32)
