@@ -254,6 +254,11 @@ PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Clo
 // (an upper bound of every length above).  The filter rejects only when
 //     min(u', v', 1-u'-v') < -delta,  delta = 64 eps (L/den) D g,   g = 2 + 1/|b'| + 2^-11/|b'|^2     (> 3x the bound)
 //     or t' < -dt,                    dt    = 64 eps D g                                              (prog.cl: t < 0 misses)
+// By the same bound a triangle with min(u', v', 1-u'-v') > +delta is CERTAIN to pass prog.cl's three edge comparisons
+// whatever the sign of t (each edge expression is positive by more than its own rounding error, and the bound covers
+// the whole t' - t difference), so only prog.cl's t is evaluated for it — every bounce ray leaves a surface at
+// t ~ +-1e-3, inside dt, so the sign of t is never taken from the filter.  prog.cl's whole test runs only on what
+// lies within delta of an edge, a ~1e-4-wide band.
 // The quadratic term makes grazing rays (|b'| < 2^-17, where b' is rounding noise) candidates unconditionally:
 // g >= 2^23 there, so delta >= 32 D L/den > |any coordinate| and dt >= 32 D > |t'|.  NaN or inf anywhere compares
 // false and the triangle stays a candidate; a record whose den is not positive (normal against the winding, or a
@@ -276,11 +281,11 @@ PT_DEV void brute_smem_filtered(const float4 *s_exact, const float4 *s_filt, int
     const float2 Pn2 = make_float2(Pn, Pn), one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
     const float2 two = make_float2(2.0f, 2.0f), q11 = make_float2(4.8828125e-4f, 4.8828125e-4f);   // 2^-11
     for (int base = 0; base < n; base += 32) {
-        unsigned mask = 0;
+        unsigned mask = 0, sure = 0;
         const float4 *f = s_filt + 7 * (base >> 1);
 #pragma unroll 1
         for (int jj = 0; jj < 16; jj += 4) {
-        unsigned m8 = 0;
+        unsigned m8 = 0, s8 = 0;
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
             const int j = jj + k4;
@@ -308,17 +313,29 @@ PT_DEV void brute_smem_filtered(const float4 *s_exact, const float4 *s_filt, int
             const bool rej_b = (fminf(fminf(u.y, v.y), q.y) < -delta.y) | (t.y < -dt.y);
             m8 |= rej_a ? 0u : 1u << (2 * k4);
             m8 |= rej_b ? 0u : 2u << (2 * k4);
+            const bool sure_a = fminf(fminf(u.x, v.x), q.x) > delta.x;
+            const bool sure_b = fminf(fminf(u.y, v.y), q.y) > delta.y;
+            s8 |= sure_a ? 1u << (2 * k4) : 0u;
+            s8 |= sure_b ? 2u << (2 * k4) : 0u;
         }
         mask |= m8 << (2 * jj);
+        sure |= s8 << (2 * jj);
         }
         const int left = n - base;
         if (left < 32) mask &= (1u << left) - 1u;
-        while (mask) {                                           // the exact test of prog.cl on the survivors, in upload order
+        while (mask) {                                           // survivors in upload order
+            const unsigned bit = mask & (0u - mask);
             const int i = base + __ffs(mask) - 1;
-            mask &= mask - 1;
-            float t;
-            const bool acc = tri_accept<false>(s_exact[3 * i], s_exact[3 * i + 1], s_exact[3 * i + 2], P, V, t, wk);
-            closest_update(best, acc, t, i);
+            mask ^= bit;
+            const float4 q0 = s_exact[3 * i], q1 = s_exact[3 * i + 1], q2 = s_exact[3 * i + 2];
+            if (sure & bit) {                                    // certainly inside: prog.cl's t decides alone (t > 0 in closest_update)
+                const V3 r1 = v3(q0), N = v3(q0.w, q1.w, q2.w);
+                closest_update(best, true, pt_div(dot(r1 - P, N), dot(V, N)), i);
+            } else {                                             // within the margin of an edge: prog.cl's whole test
+                float t;
+                const bool acc = tri_accept<false>(q0, q1, q2, P, V, t, wk);
+                closest_update(best, acc, t, i);
+            }
         }
     }
 }

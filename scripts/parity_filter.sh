@@ -1,7 +1,7 @@
 #!/bin/bash
 # parity pre-filter: tests + timing on/off
 cd /root/repo
-true
+python -m pytest tests/test_gpu_edges.py tests/test_gpu_fullsize.py tests/test_gpu_parity.py -x -q -m gpu 2>&1 | tail -3
 for f in 1 0; do
   PTB_PARITY_FILTER=$f python bench.py --steps 3 --warmup 3 2>/dev/null | python -c "
 import json,sys
