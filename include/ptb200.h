@@ -15,7 +15,9 @@
  *     error is also recorded in a sticky per-process string (ptb_last_error)
  *     and printed to stderr once; later calls become no-ops returning the error.
  *   - one in-order stream per process (the reference has one in-order
- *     cl::CommandQueue, main.cpp:506); one process drives one GPU.
+ *     cl::CommandQueue, main.cpp:506); one process drives one GPU.  Like that
+ *     queue's host side the library keeps one state per process and is NOT
+ *     thread-safe: call it from one thread (the reference does, from GLUT's).
  *   - buffer layouts are the reference's kernel ABI structs, byte for byte
  *     (prog.cl:1-35 / main.cpp:92-348): Material 80 B, Ray 32 B, Triangle 80 B,
  *     Node 48 B, Camera 80 B, colors float3 = 16 B per pixel, rnds int per pixel.

@@ -50,6 +50,7 @@ struct Staged {                        // device-internal copy of the scene, val
     ptb_mem tris_handle = 0;
     unsigned long long tris_version = ~0ull;
     int n_tris = -1;
+    unsigned max_mati = 0;             // largest Triangle::mati of the upload (checked against the materials buffer per launch)
     float4 *q0 = nullptr, *q1 = nullptr, *q2 = nullptr;   // parity layout: (r1,N.x) (r2,N.y) (r3,N.z)
     float4 *f0 = nullptr, *f1 = nullptr, *f2 = nullptr;   // fast layout: (N,r1.x) (r1.yz,mu.xy) (mu.z,mv)
     uint16_t *mati = nullptr;
@@ -149,7 +150,7 @@ MemObj *arg_mem(int k, int i) { return G.args[k][i].set ? find(G.args[k][i].mem)
 
 // ---------------------------------------------------------------- staging (AoS upload → SoA planes)
 __global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 *q1, float4 *q2,
-                             float4 *f0, float4 *f1, float4 *f2, uint16_t *mati) {
+                             float4 *f0, float4 *f1, float4 *f2, uint16_t *mati, unsigned *max_mati) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 *t = reinterpret_cast<const float4 *>(tris + i);   // 5 x 16 B per record
@@ -158,6 +159,7 @@ __global__ void k_stage_tris(const RefTriangle *tris, int n, float4 *q0, float4 
     q1[i] = make_float4(r2.x, r2.y, r2.z, N.y);
     q2[i] = make_float4(r3.x, r3.y, r3.z, N.z);
     mati[i] = tris[i].mati;
+    if (tris[i].mati > *max_mati) atomicMax(max_mati, (unsigned)tris[i].mati);
     // fast layout: barycentric gradients mu = (e2 x N)/d, mv = (N x e1)/d with d = N.(e1 x e2), in double
     double e1[3] = {(double)r2.x - r1.x, (double)r2.y - r1.y, (double)r2.z - r1.z};
     double e2[3] = {(double)r3.x - r1.x, (double)r3.y - r1.y, (double)r3.z - r1.z};
@@ -209,7 +211,9 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
         return fail(PTB_ERR_INVALID_ARGS, "trace_ray: tris_size %d exceeds the triangle buffer (%zu bytes)", n_tris, tris->bytes);
     if (n_tris > s.capacity) {
         cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
+        s.q0 = s.q1 = s.q2 = s.f0 = s.f1 = s.f2 = nullptr; s.mati = nullptr;    // a failing cudaMalloc below must not leave freed pointers behind
         s.capacity = 0;
+        s.tris_handle = 0;
         size_t cap = (size_t)n_tris + 16;
         CUDA_OK(cudaMalloc((void **)&s.q0, cap * sizeof(float4)));
         CUDA_OK(cudaMalloc((void **)&s.q1, cap * sizeof(float4)));
@@ -220,10 +224,16 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
         CUDA_OK(cudaMalloc((void **)&s.mati, cap * sizeof(uint16_t)));
         s.capacity = n_tris;
     }
+    s.max_mati = 0;
     if (n_tris > 0) {
-        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.mati);
+        // largest material index of the upload, behind the work counters (next to the seed-scan flag)
+        unsigned *max_mati = reinterpret_cast<unsigned *>(G.counters + PT_CNT_WORDS + 1);
+        CUDA_OK(cudaMemsetAsync(max_mati, 0, sizeof(unsigned), G.stream));
+        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.mati, max_mati);
         CUDA_OK(cudaGetLastError());
         G.launches++;
+        CUDA_OK(cudaMemcpyAsync(&s.max_mati, max_mati, sizeof(unsigned), cudaMemcpyDeviceToHost, G.stream));
+        CUDA_OK(cudaStreamSynchronize(G.stream));
     }
     s.tris_handle = handle;
     s.tris_version = tris->version;
@@ -346,6 +356,9 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     }
     p.sc.mats = (const RefMaterial *)mats->dptr;
     p.sc.n_mats = (int)(mats->bytes / sizeof(RefMaterial));
+    // prog.cl:322 indexes materials[] unchecked; here a record pointing past the buffer is an error, not a stray device read
+    if (tris_size > 0 && (size_t)s.max_mati >= mats->bytes / sizeof(RefMaterial))
+        return fail(PTB_ERR_INVALID_ARGS, "trace_ray: a triangle uses material %u but the materials buffer holds %zu", s.max_mati, mats->bytes / sizeof(RefMaterial));
     if (have_tree) {
         p.sc.kd_tree = (const RefNode *)tree->dptr;
         p.sc.kd_shift = (const int *)shift->dptr;
@@ -571,7 +584,7 @@ int ptb_write(ptb_mem h, size_t off, size_t bytes, const void *src) {
     MemObj *m = find(h);
     if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_write: bad handle");
     if (bytes == 0) return PTB_SUCCESS;
-    if (!src || off + bytes > m->bytes) return fail(PTB_ERR_INVALID_VALUE, "ptb_write: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
+    if (!src || off > m->bytes || bytes > m->bytes - off) return fail(PTB_ERR_INVALID_VALUE, "ptb_write: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
     int rc = flush_pending();
     if (rc) return rc;
     CUDA_OK(cudaMemcpyAsync((char *)m->dptr + off, src, bytes, cudaMemcpyHostToDevice, G.stream));
@@ -584,7 +597,7 @@ int ptb_read(ptb_mem h, size_t off, size_t bytes, void *dst) {
     MemObj *m = find(h);
     if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_read: bad handle");
     if (bytes == 0) return PTB_SUCCESS;
-    if (!dst || off + bytes > m->bytes) return fail(PTB_ERR_INVALID_VALUE, "ptb_read: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
+    if (!dst || off > m->bytes || bytes > m->bytes - off) return fail(PTB_ERR_INVALID_VALUE, "ptb_read: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
     int rc = flush_pending();
     if (rc) return rc;
     CUDA_OK(cudaMemcpyAsync(dst, (const char *)m->dptr + off, bytes, cudaMemcpyDeviceToHost, G.stream));
@@ -599,7 +612,8 @@ int ptb_ingest_mesh(ptb_mem tris_h, size_t first_tri, const float *vertices, siz
     if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_ingest_mesh: bad handle");
     if (n_faces == 0) return PTB_SUCCESS;
     if (!vertices || !indices || !mat_ids || !pos || !scale) return fail(PTB_ERR_INVALID_VALUE, "ptb_ingest_mesh: null argument");
-    if ((first_tri + n_faces) * sizeof(RefTriangle) > m->bytes)
+    const size_t cap_tris = m->bytes / sizeof(RefTriangle);
+    if (first_tri > cap_tris || n_faces > cap_tris - first_tri)
         return fail(PTB_ERR_INVALID_VALUE, "ptb_ingest_mesh: triangles [%zu,%zu) outside a %zu-byte buffer", first_tri, first_tri + n_faces, m->bytes);
     for (size_t i = 0; i < 3 * n_faces; ++i)
         if (indices[i] < 0 || (size_t)indices[i] >= n_verts)

@@ -191,3 +191,29 @@ def test_parity_prefilter_on_a_hostile_soup(ptb, seed, n):
         ptb.set_parity_filter(1)
     assert same_bits(on, off) and (rnds_on == rnds_off).all()
     assert same_bits(on, want) and (rnds_on == wrnds).all()
+
+
+def test_material_index_past_the_buffer_is_an_error_not_a_stray_read(ptb):
+    """prog.cl:322 indexes materials[] unchecked; the C-ABI refuses the launch and says why"""
+    tris = open_box() + [((0, 0, 0), (10, 0, 0), (0, 10, 0), len(MATS) + 3)]
+    surf = build(tris, 16, 8, 2)
+    ptb.set_accel(capi.ACCEL_BRUTE); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
+    s = host.scene_from_surface(surf, ptb)
+    try:
+        with pytest.raises(RuntimeError, match="material"):
+            s.render_spp(1)
+    finally:
+        ptb.clear_error()
+    ptb.finish()
+
+
+def test_read_write_range_checks_do_not_wrap(ptb):
+    h = ptb.alloc(64)
+    try:
+        for call in (lambda: ptb.lib.ptb_write(h, 2**64 - 8, 16, np.zeros(16, np.uint8).ctypes.data),
+                     lambda: ptb.lib.ptb_read(h, 2**64 - 8, 16, np.zeros(16, np.uint8).ctypes.data)):
+            assert call() == -30                       # PTB_ERR_INVALID_VALUE
+            ptb.clear_error()
+    finally:
+        ptb.clear_error()
+        ptb.release(h)
