@@ -55,6 +55,33 @@ PT_DEV void wf_push(int *queue, int *count, bool keep, int i) {
     if (keep) queue[base + __popc(m & ((1u << lane) - 1u))] = i;
 }
 
+// The same for a whole block, grouped by direction octant: the block's survivors are appended as one contiguous run in
+// which rays of one octant sit together (a counting sort over 8 buckets in shared memory), so the 32 rays a trace warp
+// fetches mostly descend the tree in the same child order.  Origins stay local (one block = 256 neighbouring paths).
+PT_DEV void wf_push_by_octant(int *queue, int *count, bool keep, int i, V3 D) {
+    __shared__ int s_cnt[8], s_off[8];
+    if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int oct = (D.x < 0.0f ? 1 : 0) | (D.y < 0.0f ? 2 : 0) | (D.z < 0.0f ? 4 : 0);
+    const unsigned peers = __match_any_sync(0xffffffffu, keep ? oct : 8);
+    int rank = 0;
+    if (keep) {
+        const int leader = __ffs(peers) - 1;
+        if (lane == leader) rank = atomicAdd(&s_cnt[oct], __popc(peers));
+        rank = __shfl_sync(peers, rank, leader) + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int o = 0; o < 8; ++o) { s_off[o] = tot; tot += s_cnt[o]; }
+        const int base = tot ? atomicAdd(count, tot) : 0;
+        for (int o = 0; o < 8; ++o) s_off[o] += base;
+    }
+    __syncthreads();
+    if (keep) queue[s_off[oct] + rank] = i;
+}
+
 // starts the next sample(s) of pixel i until a path is in flight or all samples are done; returns alive
 PT_DEV bool wf_next_sample(const RenderParams &p, int i, WfPath &w, V3 &rayP, V3 &rayD, int s_end, Work &wk) {
     const int camX = (int)p.cam.XM;
@@ -119,11 +146,12 @@ __global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const in
     Work wk = {0, 0, 0, 0, 0, 0, 0};
     bool keep = false;
     int i = 0;
+    V3 rayP = v3(0.0f, 0.0f, 0.0f), rayD = v3(0.0f, 0.0f, 1.0f);
     if (j < count) {
         i = q_in[j];
         const SceneDev &sc = p.sc;
         const float4 r0 = p.wf_ray0[i], r1 = p.wf_ray1[i];
-        V3 rayP = v3(r0.x, r0.y, r0.z), rayD = v3(r0.w, r1.x, r1.y);
+        rayP = v3(r0.x, r0.y, r0.z); rayD = v3(r0.w, r1.x, r1.y);
         const float t = r1.z;
         const int tri = __float_as_int(r1.w);
         WfPath w;
@@ -150,7 +178,8 @@ __global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const in
         else wf_finish_pixel(p, i, w);
         keep = alive;
     }
-    wf_push(q_out, n_out, keep, i);
+    if (p.wf_sort) wf_push_by_octant(q_out, n_out, keep, i, rayD);
+    else wf_push(q_out, n_out, keep, i);
     wf_flush_counters(p, wk, false);
 }
 

@@ -95,6 +95,7 @@ struct State {
     int lbvh_leaf = 4;
     int merge_prims = 1;
     int parity_filter = 1;
+    int wf_sort = 0;                   // PTB_WF_SORT=1: wavefront queues grouped by direction octant (measured slower)
     float lbvh_big = 0.25f;            // triangles spanning more than this fraction of the scene stay out of the tree (PTB_LBVH_BIG, 0 = off)
     int tex_nodes = 1;                 // node fetches through the texture pipe (PTB_TEX_NODES=0: LSU)
     int wide_bvh = 1;                  // wavefront traversal over the 4-ary collapse of the LBVH (PTB_WIDE_BVH=0: binary)
@@ -349,6 +350,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.sc.q0 = fastm ? s.f0 : s.q0; p.sc.q1 = fastm ? s.f1 : s.q1; p.sc.q2 = fastm ? s.f2 : s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
     p.sc.fq0 = s.f0; p.sc.fq1 = s.f1; p.sc.fq2 = s.f2;
     p.parity_filter = G.parity_filter;
+    p.wf_sort = G.wf_sort;
     if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
         rc = ensure_prims();
         if (rc) return rc;
@@ -488,6 +490,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_BRUTE_MAX"))) G.brute_max = atoi(env);
     if ((env = getenv("PTB_MERGE_PRIMS"))) G.merge_prims = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_PARITY_FILTER"))) G.parity_filter = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_WF_SORT"))) G.wf_sort = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);

@@ -2,7 +2,8 @@
 run() { python bench.py --workload $1 --spp $2 --steps 2 --warmup 3 --pipeline ${3:-wavefront} --no-cpu-baseline --no-e2e 2>&1 | tail -1 | python -c "
 import sys,json
 d=json.loads(sys.stdin.readline()); r=d['roofline']; print(round(d['value']), 'B=%.1f T=%.1f' % (r['box_tests_per_ray'], r['tri_tests_per_ray']))"; }
-for steps in 4 2; do for leaf in 8 4; do
-  echo -n "spheres100k node_steps=$steps leaf_min=$leaf : "; PTB_WF_NODE_STEPS=$steps PTB_WF_LEAF_MIN=$leaf run spheres100k_1080p_256spp_d4 8
-  echo -n "grid1m node_steps=$steps leaf_min=$leaf : "; PTB_WF_NODE_STEPS=$steps PTB_WF_LEAF_MIN=$leaf run grid1m_4k_64spp_d4 8
-done; done
+python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py -x -q -m gpu -k "wavefront or lbvh or pipeline" 2>&1 | tail -2
+for sort in 0 1; do
+  echo -n "spheres100k sort=$sort : "; PTB_WF_SORT=$sort run spheres100k_1080p_256spp_d4 16
+  echo -n "grid1m sort=$sort : "; PTB_WF_SORT=$sort run grid1m_4k_64spp_d4 8
+done
