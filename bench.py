@@ -11,6 +11,9 @@ executed iteration of the bounce loop (prog.cl:317-319), counted by the kernel i
 N > 1 (torchrun, one rank per GPU): spp-split — every rank renders `spp` samples of every pixel with
 its own seed set into a sum buffer, then ONE NCCL reduce(SUM) to rank 0 + a sum/(N*spp) resolve, all
 inside the timed step (weak scaling: per-GPU work fixed, the job is an N*spp-sample image).
+`--split tile` (BASELINE configs[4]): the SAME frame x spp job is cut into bands of 8 scanlines dealt
+round-robin to the ranks, every pixel keeps the reference's seed, and the disjoint pixel sets are summed
+at rank 0 by one NCCL reduce per step (strong scaling: total work fixed; the image is bitwise the 1-GPU one).
 """
 import argparse
 import json
@@ -36,6 +39,7 @@ WORKLOADS = {
     "cornell_512_16spp_d4": ("cornell", 512, 512, 16, 4),
     "spheres100k_1080p_256spp_d4": ("spheres100k", 1920, 1080, 256, 4),
     "grid1m_4k_64spp_d4": ("grid1m", 3840, 2160, 64, 4),
+    "grid1m_4k_8192spp_d4": ("grid1m", 3840, 2160, 8192, 4),     # BASELINE configs[4]; use with --split tile (and --spp for a prefix)
 }
 
 
@@ -52,6 +56,9 @@ def parse():
     ap.add_argument("--math", default="fast", choices=["fast", "parity"])
     ap.add_argument("--accel", default="auto", choices=["auto", "brute", "refbvh", "lbvh"])
     ap.add_argument("--pipeline", default="auto", choices=["auto", "megakernel", "wavefront"])
+    ap.add_argument("--split", default="spp", choices=["spp", "tile"],
+                    help="N > 1: spp (weak scaling: every rank renders spp samples of every pixel, reduce(SUM)) or tile (strong scaling: "
+                         "the frame's bands of 8 scanlines round-robin over the ranks with the reference's seeds, bitwise the 1-GPU image)")
     ap.add_argument("--ref-spp", type=int, default=0, help="reference arm: samples per step (default: sized to a few seconds)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -201,9 +208,11 @@ def main():
     scene.build_trees = args.accel == "refbvh"
     t0 = time.time()
     build_scene(scene_name, scene)
-    scene.init_Scene(W, H, seed_skip=multigpu.rank_seed_skip(rank, W, H))
+    tile = world > 1 and args.split == "tile"
+    seed_skip = 0 if tile else multigpu.rank_seed_skip(rank, W, H)      # tile-split: every pixel keeps the reference's own seed
+    scene.init_Scene(W, H, seed_skip=seed_skip)
     frame = multigpu.DeviceFrame(ptb, W, H, dev)
-    seeds_host = torch.from_numpy(host.minstd_rand0_seeds(W * H, multigpu.rank_seed_skip(rank, W, H))).pin_memory()
+    seeds_host = torch.from_numpy(host.minstd_rand0_seeds(W * H, seed_skip)).pin_memory()
     frame.rnds.copy_(seeds_host)
     frame.attach(scene)
     scene.upload_Triangles()
@@ -216,7 +225,9 @@ def main():
     setup_s = time.time() - t0
     n_tris = len(scene.tris)
     accel_used = {1: "brute(shared memory)", 2: "reference trees", 3: "lbvh"}[ptb.get_accel()]
-    ptb.set_accumulate_sum(1 if world > 1 else 0)
+    ptb.set_accumulate_sum(1 if world > 1 and not tile else 0)
+    if tile:
+        ptb.set_pixel_shard(rank, world, multigpu.shard_group(W))
 
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
@@ -226,8 +237,8 @@ def main():
             frame.colors.zero_()
         scene.render_spp(spp)
         if world > 1:
-            multigpu.reduce_sum_to_root(frame.colors)
-            if rank == 0:
+            multigpu.reduce_sum_to_root(frame.colors)     # tile-split: disjoint pixel sets, x + 0 == x, so the sum is an exact gather
+            if rank == 0 and not tile:
                 ptb.resolve_sum(frame.h_colors, spp * world)
 
     def barrier():
@@ -370,13 +381,15 @@ def main():
     if rank == 0:
         line = {
             "metric": "path-trace throughput", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "spp_per_s": spp * world * args.steps / (total_ms * 1e-3),
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tile else "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "spp_per_s": spp * (1 if tile else world) * args.steps / (total_ms * 1e-3),
             "rays_per_step": total_rays / args.steps,
-            "config": {"workload": args.workload, "width": W, "height": H, "spp_per_gpu_per_step": spp, "depth": depth, "triangles": n_tris,
+            "config": {"workload": args.workload, "width": W, "height": H, "spp_per_gpu_per_step": spp, "split": (args.split if world > 1 else None), "depth": depth, "triangles": n_tris,
                        "scan_primitives": int(ptb.scan_prims()) if accel_used.startswith("brute") and args.math == "fast" else None,
                        "accel": accel_used, "math": args.math, "pipeline": args.pipeline,
-                       "parallelism": "single GPU" if world == 1 else f"spp-split x{world} + NCCL reduce(SUM) of the accumulation buffer per step",
+                       "parallelism": "single GPU" if world == 1 else
+                       (f"tile-split x{world} (bands of 8 scanlines round-robin, reference seeds) + NCCL reduce of the disjoint pixel sets per step" if tile
+                        else f"spp-split x{world} + NCCL reduce(SUM) of the accumulation buffer per step"),
                        "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s,
                        "lbvh": ptb.accel_stats() if accel_used == "lbvh" else None},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "bit_exact_flavour": exact,
