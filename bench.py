@@ -59,6 +59,8 @@ def parse():
     ap.add_argument("--split", default="spp", choices=["spp", "tile"],
                     help="N > 1: spp (weak scaling: every rank renders spp samples of every pixel, reduce(SUM)) or tile (strong scaling: "
                          "the frame's bands of 8 scanlines round-robin over the ranks with the reference's seeds, bitwise the 1-GPU image)")
+    ap.add_argument("--emulate-shard", type=int, default=0, metavar="N",
+                    help="N = 1 GPU only, profiling aid: render just rank 0's share of an N-way tile split (what one GPU of --gpus N --split tile does)")
     ap.add_argument("--ref-spp", type=int, default=0, help="reference arm: samples per step (default: sized to a few seconds)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -228,6 +230,8 @@ def main():
     ptb.set_accumulate_sum(1 if world > 1 and not tile else 0)
     if tile:
         ptb.set_pixel_shard(rank, world, multigpu.shard_group(W))
+    elif world == 1 and args.emulate_shard > 1:
+        ptb.set_pixel_shard(0, args.emulate_shard, multigpu.shard_group(W))
 
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
@@ -384,7 +388,7 @@ def main():
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tile else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "spp_per_s": spp * (1 if tile else world) * args.steps / (total_ms * 1e-3),
             "rays_per_step": total_rays / args.steps,
-            "config": {"workload": args.workload, "width": W, "height": H, "spp_per_gpu_per_step": spp, "split": (args.split if world > 1 else None), "depth": depth, "triangles": n_tris,
+            "config": {"workload": args.workload, "width": W, "height": H, "spp_per_gpu_per_step": spp, "split": (args.split if world > 1 else None), "emulate_shard": args.emulate_shard or None, "depth": depth, "triangles": n_tris,
                        "scan_primitives": int(ptb.scan_prims()) if accel_used.startswith("brute") and args.math == "fast" else None,
                        "accel": accel_used, "math": args.math, "pipeline": args.pipeline,
                        "parallelism": "single GPU" if world == 1 else

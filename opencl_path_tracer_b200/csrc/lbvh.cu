@@ -25,7 +25,7 @@
 //   n2 = (L.lo.z, L.hi.z, R.lo.z, R.hi.z)  n3 = (bits(left link), bits(right link), 0, 0)
 // link >= 0: node index.  link < 0: leaf, ~link = (first << 3) | (count-1) in Morton order.
 // Wide node layout (8 x float4 = one 128-byte line): lo.x[4] hi.x[4] lo.y[4] hi.y[4] lo.z[4] hi.z[4] links[4] pad;
-// an empty slot has an all-NaN box, which no slab test accepts.
+// an empty slot has an inverted infinite box (lo = +inf, hi = -inf), which no slab test accepts.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
@@ -285,14 +285,16 @@ __global__ void k_emit4(int n, int leaf_size, float eps, const int2 *range, cons
             s[ns++] = t;
         }
     }
-    const float qnan = __int_as_float(0x7fc00000);
+    // empty slots: an inverted infinite box (entry +inf, exit -inf for every direction sign: never hit; NaNs would be
+    // dropped by the min/max of the slab test)
+    const float pinf = __int_as_float(0x7f800000), ninf = __int_as_float(0xff800000);
     float v[6][4];
     int link[4];
     for (int k = 0; k < 4; ++k) {
         const bool on = k < ns;
-        v[0][k] = on ? s[k].lo.x - eps : qnan; v[1][k] = on ? s[k].hi.x + eps : qnan;
-        v[2][k] = on ? s[k].lo.y - eps : qnan; v[3][k] = on ? s[k].hi.y + eps : qnan;
-        v[4][k] = on ? s[k].lo.z - eps : qnan; v[5][k] = on ? s[k].hi.z + eps : qnan;
+        v[0][k] = on ? s[k].lo.x - eps : pinf; v[1][k] = on ? s[k].hi.x + eps : ninf;
+        v[2][k] = on ? s[k].lo.y - eps : pinf; v[3][k] = on ? s[k].hi.y + eps : ninf;
+        v[4][k] = on ? s[k].lo.z - eps : pinf; v[5][k] = on ? s[k].hi.z + eps : ninf;
         link[k] = on ? s[k].link : leaf_link(0, 1);
     }
     float4 *o = bvh4 + 8 * (size_t)id4[i];

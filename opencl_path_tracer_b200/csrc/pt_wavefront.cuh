@@ -117,8 +117,11 @@ PT_DEV void wf_flush_counters(const RenderParams &p, const Work &wk, bool count)
 }
 
 // ---------------------------------------------------------------- init: first camera ray of every selected pixel
-__global__ void __launch_bounds__(256) k_wf_init(const RenderParams p) {
+// `subs` interleaved sub-wavefronts (launch_wavefront): block b feeds sub b % subs, whose first queue starts at
+// wf_queue[0] + sub * sub_cap and whose control words are wf_ctrl + 4 * sub
+__global__ void __launch_bounds__(256) k_wf_init(const RenderParams p, const int subs, const int sub_cap) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int sub = blockIdx.x % subs;
     const int n = p.W * p.H;
     Work wk = {0, 0, 0, 0, 0, 0, 0};
     bool keep = false;
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(256) k_wf_init(const RenderParams p) {
         if (keep) { wf_store_ray(p, i, P, D); wf_store_state(p, i, w); }
         else wf_finish_pixel(p, i, w);
     }
-    wf_push(p.wf_queue[0], p.wf_ctrl + 0, keep, i);
+    wf_push(p.wf_queue[0] + (size_t)sub * sub_cap, p.wf_ctrl + 4 * sub, keep, i);
     wf_flush_counters(p, wk, false);
 }
 
@@ -232,6 +235,7 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
     V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
     Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
     float ix = 0.0f, iy = 0.0f, iz = 0.0f, ox = 0.0f, oy = 0.0f, oz = 0.0f;
+    int nx = 0, ny = 0, nz = 0;                          // row of the NEAR plane per axis: 0 = lo (direction >= 0), 1 = hi
 #ifdef WF_DEBUG_STATES
     unsigned dbgN = 0, dbgL = 0, dbgF = 0, dbgP = 0, dbgI = 0;
 #endif
@@ -263,6 +267,7 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     P = v3(r0.x, r0.y, r0.z); D = v3(r0.w, r1.x, r1.y);
                     ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
                     ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
+                    nx = ix < 0.0f ? 1 : 0; ny = iy < 0.0f ? 1 : 0; nz = iz < 0.0f ? 1 : 0;
                     best.t = PT_NO_HIT; best.tri = 0x7fffffff;
 #if !PT_PARITY
                     if (n_big_pairs > 0) {                            // packed scan over the merged outliers, then primitive -> upload index
@@ -298,25 +303,29 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     }
                 }
                 if (WIDE && st == WF_NODE) {
-                    // 4-ary node (lbvh.cu): four slab tests, hits sorted by entry distance, nearest visited, rest pushed far-to-near
+                    // 4-ary node (lbvh.cu): four slab tests, hits sorted by entry distance, nearest visited, rest pushed far-to-near.
+                    // The near / far plane of every axis is picked by the SIGN of the ray direction when the row is fetched
+                    // (rows 0/1 = lo.x/hi.x of the four children, 2/3 = y, 4/5 = z), not by a min/max per child and axis:
+                    // fma(X, ix, -ox) is monotonic in X, so the picked values ARE min(a, b) / max(a, b) of the old test.
+                    // Hit <=> max(entry * (1 - 4e-6), 0) <= min(exit * (1 + 4e-6), best.t); the clamped entry is the sort / cull key.
                     const float4 *nd = sc.bvh4 + 8 * (size_t)link;
-                    float4 X0, X1, Y0, Y1, Z0, Z1, LK, pad_;
+                    float4 Xn, Xf, Yn, Yf, Zn, Zf, LK;
                     if (sc.bvh4_tex) {
                         const int t_ = 8 * link;
-                        X0 = tex1Dfetch<float4>(sc.bvh4_tex, t_); X1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 1);
-                        Y0 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2); Y1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 3);
-                        Z0 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4); Z1 = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 5);
+                        Xn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + nx); Xf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + (nx ^ 1));
+                        Yn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + ny); Yf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + (ny ^ 1));
+                        Zn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + nz); Zf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + (nz ^ 1));
                         LK = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 6);
                     } else {
-                        ldg8(nd, X0, X1); ldg8(nd + 2, Y0, Y1); ldg8(nd + 4, Z0, Z1); ldg8(nd + 6, LK, pad_);
+                        Xn = ldg4(nd + nx); Xf = ldg4(nd + (nx ^ 1)); Yn = ldg4(nd + 2 + ny); Yf = ldg4(nd + 2 + (ny ^ 1));
+                        Zn = ldg4(nd + 4 + nz); Zf = ldg4(nd + 4 + (nz ^ 1)); LK = ldg4(nd + 6);
                     }
                     if (COUNT) wk.box += 4;
                     float d0, d1, d2, d3;
-#define WF_SLAB(dk, c) do { float a_ = fmaf(X0.c, ix, -ox), b_ = fmaf(X1.c, ix, -ox); float l0_ = fminf(a_, b_), l1_ = fmaxf(a_, b_);          \
-                            a_ = fmaf(Y0.c, iy, -oy); b_ = fmaf(Y1.c, iy, -oy); l0_ = fmaxf(l0_, fminf(a_, b_)); l1_ = fminf(l1_, fmaxf(a_, b_)); \
-                            a_ = fmaf(Z0.c, iz, -oz); b_ = fmaf(Z1.c, iz, -oz); l0_ = fmaxf(l0_, fminf(a_, b_)); l1_ = fminf(l1_, fmaxf(a_, b_)); \
-                            const float e_ = l0_ * 0.999996f;                                                                                 \
-                            dk = ((l0_ <= l1_ * 1.000004f) & (l1_ >= 0.0f) & (e_ <= best.t)) ? e_ : PT_NO_HIT; } while (0)
+#define WF_SLAB(dk, c) do { float lo_ = fmaxf(fmaxf(fmaf(Xn.c, ix, -ox), fmaf(Yn.c, iy, -oy)), fmaf(Zn.c, iz, -oz));                 \
+                            float hi_ = fminf(fminf(fmaf(Xf.c, ix, -ox), fmaf(Yf.c, iy, -oy)), fmaf(Zf.c, iz, -oz));                 \
+                            lo_ = fmaxf(lo_ * 0.999996f, 0.0f); hi_ = fminf(hi_ * 1.000004f, best.t);                                \
+                            dk = lo_ <= hi_ ? lo_ : PT_NO_HIT; } while (0)
                     WF_SLAB(d0, x); WF_SLAB(d1, y); WF_SLAB(d2, z); WF_SLAB(d3, w);
 #undef WF_SLAB
                     int k0 = __float_as_int(LK.x), k1 = __float_as_int(LK.y), k2 = __float_as_int(LK.z), k3 = __float_as_int(LK.w);
@@ -386,11 +395,40 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
 }
 
 // ---------------------------------------------------------------- host side: the iteration loop
+// The frame's paths are dealt to WF_SUBS independent sub-wavefronts (blocks of 256 pixel ids, round-robin), each with its own
+// queues and its own stream.  The persistent trace kernel of one sub-wavefront fills the machine; when its queue runs dry its
+// blocks exit one by one, and the other sub-wavefront's shade / trace blocks move into the freed slots instead of the SMs
+// idling until the last long ray of the launch is done (the tail is about one ray latency, ~40 us: 7 % of a 2 M-path
+// iteration, 20 % of a 1 M-path one — the 8-GPU tile split).  Paths never move between sub-wavefronts and a pixel's samples
+// stay sequential, so the image does not depend on the number of sub-wavefronts.
+#define WF_SUBS_MAX 4
+struct WfStreams { cudaStream_t s[WF_SUBS_MAX]; cudaEvent_t fork, join[WF_SUBS_MAX]; int *h_count; bool ok; };
+static WfStreams &wf_streams() {
+    static WfStreams w = [] {
+        WfStreams t{};
+        t.ok = true;
+        for (int j = 1; j < WF_SUBS_MAX; ++j) {
+            t.ok &= cudaStreamCreateWithFlags(&t.s[j], cudaStreamNonBlocking) == cudaSuccess;
+            t.ok &= cudaEventCreateWithFlags(&t.join[j], cudaEventDisableTiming) == cudaSuccess;
+        }
+        t.ok &= cudaEventCreateWithFlags(&t.fork, cudaEventDisableTiming) == cudaSuccess;
+        t.ok &= cudaMallocHost((void **)&t.h_count, WF_SUBS_MAX * sizeof(int)) == cudaSuccess;
+        return t;
+    }();
+    return w;
+}
+
 int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     const int n = p.W * p.H;
     int launches = 0;
-    cudaMemsetAsync(p.wf_ctrl, 0, 4 * sizeof(int), st);
-    k_wf_init<<<(n + 255) / 256, 256, 0, st>>>(p);
+    WfStreams &ws = wf_streams();
+    static const int want_subs = getenv("PTB_WF_SUBS") ? atoi(getenv("PTB_WF_SUBS")) : 2;
+    const int init_blocks = (n + 255) / 256;
+    int subs = ws.ok ? (want_subs < 1 ? 1 : want_subs > WF_SUBS_MAX ? WF_SUBS_MAX : want_subs) : 1;
+    if (subs > init_blocks) subs = init_blocks > 0 ? init_blocks : 1;
+    const int sub_cap = ((init_blocks + subs - 1) / subs) * 256;          // queue slots per sub-wavefront (ptb_abi.cu sizes the queues for it)
+    cudaMemsetAsync(p.wf_ctrl, 0, 4 * WF_SUBS_MAX * sizeof(int), st);
+    k_wf_init<<<init_blocks, 256, 0, st>>>(p, subs, sub_cap);
     ++launches;
     int sms = 148, dev = 0;
     cudaGetDevice(&dev);
@@ -398,42 +436,67 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     // persistent grid: exactly as many blocks as are resident at once (a block that has to wait for a slot would start
     // after the queue is drained and add a tail); 54-64 registers and 16-20 KB of shared memory give 8-9 per SM
     static const int want_per_sm = getenv("PTB_WF_BLOCKS") ? atoi(getenv("PTB_WF_BLOCKS")) : 9;
-    const bool wide_ = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+    const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
     int occ = 0;
     if (p.count_work) {
-        if (wide_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, true>, PT_BLOCK, 0);
+        if (wide) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, true>, PT_BLOCK, 0);
         else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, PT_BLOCK, 0);
     } else {
-        if (wide_) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, true>, PT_BLOCK, 0);
+        if (wide) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, true>, PT_BLOCK, 0);
         else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, PT_BLOCK, 0);
     }
     const int per_sm = occ > 0 && occ < want_per_sm ? occ : want_per_sm;
     const int trace_blocks = sms * per_sm;
+    static const int3 tune = make_int3(getenv("PTB_WF_FETCH_MIN") ? atoi(getenv("PTB_WF_FETCH_MIN")) : WF_FETCH_MIN,
+                                       getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 4,
+                                       getenv("PTB_WF_NODE_STEPS") ? atoi(getenv("PTB_WF_NODE_STEPS")) : PT_SCHED_NODE_STEPS);
     const long long max_iters = (long long)p.spp * (p.iterations > 0 ? p.iterations : 0);
-    int host_count = n;
+    cudaStream_t sj[WF_SUBS_MAX];
+    int host_count[WF_SUBS_MAX];
+    bool live[WF_SUBS_MAX];
+    sj[0] = st;
+    if (subs > 1) cudaEventRecord(ws.fork, st);
+    for (int j = 0; j < subs; ++j) {
+        if (j > 0) { sj[j] = ws.s[j]; cudaStreamWaitEvent(sj[j], ws.fork, 0); }
+        host_count[j] = sub_cap;
+        live[j] = true;
+    }
     for (long long it = 0; it < max_iters; ++it) {
         const int a = (int)(it & 1), b = a ^ 1;
-        // next queue length and the fetch cursor start at zero
-        cudaMemsetAsync(p.wf_ctrl + b, 0, sizeof(int), st);
-        cudaMemsetAsync(p.wf_ctrl + 2, 0, sizeof(int), st);
-        const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
-        static const int3 tune = make_int3(getenv("PTB_WF_FETCH_MIN") ? atoi(getenv("PTB_WF_FETCH_MIN")) : WF_FETCH_MIN,
-                                           getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 4,
-                                           getenv("PTB_WF_NODE_STEPS") ? atoi(getenv("PTB_WF_NODE_STEPS")) : PT_SCHED_NODE_STEPS);
-        if (p.count_work) {
-            if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
-            else k_wf_trace<true, false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
-        } else {
-            if (wide) k_wf_trace<false, true><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
-            else k_wf_trace<false, false><<<trace_blocks, PT_BLOCK, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_ctrl + 2, tune);
+        bool any = false;
+        for (int j = 0; j < subs; ++j) {
+            if (!live[j]) continue;
+            any = true;
+            int *ctrl = p.wf_ctrl + 4 * j;
+            int *qa = p.wf_queue[a] + (size_t)j * sub_cap, *qb = p.wf_queue[b] + (size_t)j * sub_cap;
+            // next queue length and the fetch cursor start at zero
+            cudaMemsetAsync(ctrl + b, 0, sizeof(int), sj[j]);
+            cudaMemsetAsync(ctrl + 2, 0, sizeof(int), sj[j]);
+            if (p.count_work) {
+                if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else k_wf_trace<true, false><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+            } else {
+                if (wide) k_wf_trace<false, true><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else k_wf_trace<false, false><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+            }
+            k_wf_shade<<<(host_count[j] + 255) / 256, 256, 0, sj[j]>>>(p, qa, ctrl + a, qb, ctrl + b);
+            launches += 2;
         }
-        k_wf_shade<<<(host_count + 255) / 256, 256, 0, st>>>(p, p.wf_queue[a], p.wf_ctrl + a, p.wf_queue[b], p.wf_ctrl + b);
-        launches += 2;
-        if ((it & 15) == 15) {                     // every 16 iterations: learn the real queue length (shrinks the grids, ends early)
-            cudaMemcpyAsync(&host_count, p.wf_ctrl + b, sizeof(int), cudaMemcpyDeviceToHost, st);
-            cudaStreamSynchronize(st);
-            if (host_count == 0) break;
+        if (!any) break;
+        if ((it & 15) == 15) {                     // every 16 iterations: learn the real queue lengths (shrinks the grids, ends early)
+            for (int j = 0; j < subs; ++j)
+                if (live[j]) cudaMemcpyAsync(ws.ok ? ws.h_count + j : host_count + j, p.wf_ctrl + 4 * j + b, sizeof(int), cudaMemcpyDeviceToHost, sj[j]);
+            for (int j = 0; j < subs; ++j) {
+                if (!live[j]) continue;
+                cudaStreamSynchronize(sj[j]);
+                if (ws.ok) host_count[j] = ws.h_count[j];
+                if (host_count[j] == 0) live[j] = false;
+            }
         }
+    }
+    for (int j = 1; j < subs; ++j) {               // join: the caller's stream continues after every sub-wavefront
+        cudaEventRecord(ws.join[j], sj[j]);
+        cudaStreamWaitEvent(st, ws.join[j], 0);
     }
     return launches;
 }

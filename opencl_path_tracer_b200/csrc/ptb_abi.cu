@@ -436,21 +436,23 @@ int run_render(const RenderParams &p) {
     return PTB_SUCCESS;
 }
 
-// wavefront pipeline: 136 bytes of scratch per pixel (ray 32, path state 96, two queue slots 8)
+// wavefront pipeline: 136 bytes of scratch per pixel (ray 32, path state 96, two queue slots 8); each queue carries
+// WF_QUEUE_SLACK extra bytes because its sub-wavefronts' shares are rounded up to whole blocks of 256 pixel ids
+#define WF_QUEUE_SLACK 8192
 int run_wavefront(RenderParams &p) {
     const size_t n = (size_t)p.W * p.H;
     if (n > G.wf_pixels) {
         cudaFree(G.wf_blob);
         G.wf_blob = nullptr; G.wf_pixels = 0;
-        CUDA_OK(cudaMalloc(&G.wf_blob, n * 136 + 256));
+        CUDA_OK(cudaMalloc(&G.wf_blob, n * 136 + 2 * WF_QUEUE_SLACK + 256));
         G.wf_pixels = n;
     }
     char *b = (char *)G.wf_blob;
     p.wf_ray0 = (float4 *)b; b += n * 16;
     p.wf_ray1 = (float4 *)b; b += n * 16;
     p.wf_state = (float4 *)b; b += n * 96;
-    p.wf_queue[0] = (int *)b; b += n * 4;
-    p.wf_queue[1] = (int *)b; b += n * 4;
+    p.wf_queue[0] = (int *)b; b += n * 4 + WF_QUEUE_SLACK;
+    p.wf_queue[1] = (int *)b; b += n * 4 + WF_QUEUE_SLACK;
     p.wf_ctrl = (int *)b;
     int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_wavefront(p, G.stream) : pt_fast::launch_wavefront(p, G.stream);
     CUDA_OK(cudaGetLastError());
