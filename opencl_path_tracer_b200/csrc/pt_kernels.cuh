@@ -832,14 +832,17 @@ __global__ void __launch_bounds__(128) k_closest_hit(const RenderParams p, const
     out[i] = make_float2(hit ? best.t : -1.0f, __int_as_float(hit ? best.tri : -1));
 }
 // the wavefront trace kernel on an arbitrary ray list: rays -> its ray records + an identity queue, and back
-__global__ void k_ch_pack(const RefRay *rays, size_t n, float4 *ray0, float4 *ray1, int *queue, int *ctrl) {
+__global__ void k_ch_pack(const RenderParams p, const RefRay *rays, size_t n, float4 *ray0, float4 *ray1, int *queue, int *ctrl) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) { ctrl[0] = (int)n; ctrl[1] = 0; ctrl[2] = 0; ctrl[3] = 0; }
     if (i >= n) return;
     const float4 *r = reinterpret_cast<const float4 *>(rays + i);
     const float4 a = r[0], b = r[1];
+    Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+    Work wk = {0, 0, 0, 0, 0, 0, 0};
+    lbvh_big_scan<false>(p.sc, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), best, wk);     // the outlier list, as the path kernels do where a ray is created
     ray0[i] = make_float4(a.x, a.y, a.z, b.x);
-    ray1[i] = make_float4(b.y, b.z, PT_NO_HIT, __int_as_float(0x7fffffff));
+    ray1[i] = make_float4(b.y, b.z, best.t, __int_as_float(best.tri));
     queue[i] = (int)i;
 }
 __global__ void k_ch_unpack(const float4 *ray1, size_t n, float2 *out) {
@@ -910,7 +913,7 @@ int launch_closest_hit(const RenderParams &p0, const RefRay *rays, size_t n, flo
         p.wf_ray1 = (float4 *)b; b += n * 16;
         p.wf_queue[0] = (int *)b; b += n * 4;
         p.wf_ctrl = (int *)b;
-        k_ch_pack<<<blocks, 128, 0, st>>>(rays, n, p.wf_ray0, p.wf_ray1, p.wf_queue[0], p.wf_ctrl);
+        k_ch_pack<<<blocks, 128, 0, st>>>(p, rays, n, p.wf_ray0, p.wf_ray1, p.wf_queue[0], p.wf_ctrl);
         int sms = 148, dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -39,9 +39,54 @@ PT_DEV void wf_load_state(const RenderParams &p, int i, WfPath &w) {
     w.acc = v3(e.x, e.y, e.z); w.s = __float_as_int(e.w);
     w.depth = __float_as_int(f.x); w.ps.in = __float_as_int(f.y) != 0;
 }
-PT_DEV void wf_store_ray(const RenderParams &p, int i, V3 P, V3 D) {
+PT_DEV void wf_store_ray(const RenderParams &p, int i, V3 P, V3 D, const Closest &best) {
     p.wf_ray0[i] = make_float4(P.x, P.y, P.z, D.x);
-    p.wf_ray1[i] = make_float4(D.y, D.z, PT_NO_HIT, __int_as_float(0x7fffffff));
+    p.wf_ray1[i] = make_float4(D.y, D.z, best.t, __int_as_float(best.tri));
+}
+
+// The LBVH's outlier list (room walls, emitter quads: lbvh.cu step 2) is scanned by the kernel that CREATES a ray — k_wf_init /
+// k_wf_shade, full warps — and its result travels in the ray record as the traversal's initial best hit.  Inside the trace
+// kernel the same scan ran whenever a few lanes refilled, at 11 of 32 lanes (profiles/r01_wf_trace_v6.txt: 15 % of its
+// instructions).  Fast flavour: the outliers as merged quads in the pair layout of brute_smem_prims (pt_kernels.cuh), staged
+// in shared memory by the block; parity flavour and the counting build: the plain triangles.
+#define WF_BIG_SMEM (7 * (LBVH_BIG_MAX / 2))
+PT_DEV int wf_stage_big(const RenderParams &p, float4 *s_big) {
+#if !PT_PARITY
+    const SceneDev &sc = p.sc;
+    const int n_big_pairs = (p.count_work || p.accel != PT_ACCEL_LBVH) ? 0 : (sc.n_big_prims + 1) >> 1;
+    for (int j = threadIdx.x; j < n_big_pairs; j += blockDim.x) {
+        const int ia = 2 * j, ib = 2 * j + 1;
+        const bool hb = ib < sc.n_big_prims;
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        const float4 A0 = ldg4(sc.bq0 + ia), A1 = ldg4(sc.bq1 + ia), A2 = ldg4(sc.bq2 + ia);
+        const float4 B0 = hb ? ldg4(sc.bq0 + ib) : z, B1 = hb ? ldg4(sc.bq1 + ib) : z, B2 = hb ? ldg4(sc.bq2 + ib) : z;
+        const float2 sa = __ldg(sc.big_ab + ia), sb = hb ? __ldg(sc.big_ab + ib) : make_float2(1.0f, 0.0f);
+        s_big[7 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
+        s_big[7 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
+        s_big[7 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
+        s_big[7 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
+        s_big[7 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
+        s_big[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
+        s_big[7 * j + 6] = make_float4(-sa.x, -sb.x, -sa.y, -sb.y);
+    }
+    __syncthreads();
+    return n_big_pairs;
+#else
+    return 0;
+#endif
+}
+PT_DEV void wf_big_scan(const RenderParams &p, const float4 *s_big, int n_big_pairs, V3 P, V3 D, Closest &best, Work &wk) {
+    best.t = PT_NO_HIT; best.tri = 0x7fffffff;
+    if (p.accel != PT_ACCEL_LBVH) return;
+#if !PT_PARITY
+    if (n_big_pairs > 0) {                            // packed scan over the merged outliers, then primitive -> upload index
+        brute_smem_prims<2>(s_big, n_big_pairs, P, D, best);
+        if (best.t < PT_NO_HIT) best.tri = __ldg(p.sc.big_rep + best.tri);
+        return;
+    }
+#endif
+    if (p.count_work) lbvh_big_scan<true>(p.sc, P, D, best, wk);
+    else lbvh_big_scan<false>(p.sc, P, D, best, wk);
 }
 
 // append `i` to the output queue for the lanes with keep == true: one atomic per warp
@@ -124,6 +169,8 @@ __global__ void __launch_bounds__(256) k_wf_init(const RenderParams p, const int
     const int sub = blockIdx.x % subs;
     const int n = p.W * p.H;
     Work wk = {0, 0, 0, 0, 0, 0, 0};
+    __shared__ float4 s_big[WF_BIG_SMEM];
+    const int n_big_pairs = wf_stage_big(p, s_big);
     bool keep = false;
     if (i < n && (p.shard_n <= 1 || ((i / p.shard_group) % p.shard_n) == p.shard_rank)) {
         WfPath w;
@@ -134,11 +181,15 @@ __global__ void __launch_bounds__(256) k_wf_init(const RenderParams p, const int
         path_reset(w.ps);
         V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
         keep = wf_next_sample(p, i, w, P, D, p.sample0 + p.spp, wk);
-        if (keep) { wf_store_ray(p, i, P, D); wf_store_state(p, i, w); }
-        else wf_finish_pixel(p, i, w);
+        if (keep) {
+            Closest best;
+            wf_big_scan(p, s_big, n_big_pairs, P, D, best, wk);
+            wf_store_ray(p, i, P, D, best);
+            wf_store_state(p, i, w);
+        } else wf_finish_pixel(p, i, w);
     }
     wf_push(p.wf_queue[0] + (size_t)sub * sub_cap, p.wf_ctrl + 4 * sub, keep, i);
-    wf_flush_counters(p, wk, false);
+    wf_flush_counters(p, wk, p.count_work != 0);
 }
 
 // ---------------------------------------------------------------- shade: one thread per queued path
@@ -147,6 +198,8 @@ __global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const in
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int count = *n_in;
     Work wk = {0, 0, 0, 0, 0, 0, 0};
+    __shared__ float4 s_big[WF_BIG_SMEM];
+    const int n_big_pairs = wf_stage_big(p, s_big);
     bool keep = false;
     int i = 0;
     V3 rayP = v3(0.0f, 0.0f, 0.0f), rayD = v3(0.0f, 0.0f, 1.0f);
@@ -177,13 +230,17 @@ __global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const in
             wk.samples++;
             alive = wf_next_sample(p, i, w, rayP, rayD, p.sample0 + p.spp, wk);
         }
-        if (alive) { wf_store_ray(p, i, rayP, rayD); wf_store_state(p, i, w); }
-        else wf_finish_pixel(p, i, w);
+        if (alive) {
+            Closest best;
+            wf_big_scan(p, s_big, n_big_pairs, rayP, rayD, best, wk);
+            wf_store_ray(p, i, rayP, rayD, best);
+            wf_store_state(p, i, w);
+        } else wf_finish_pixel(p, i, w);
         keep = alive;
     }
     if (p.wf_sort) wf_push_by_octant(q_out, n_out, keep, i, rayD);
     else wf_push(q_out, n_out, keep, i);
-    wf_flush_counters(p, wk, false);
+    wf_flush_counters(p, wk, p.count_work != 0);
 }
 
 // ---------------------------------------------------------------- trace: persistent warps over the queue
@@ -209,27 +266,6 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
     __shared__ int2 s_stack[WF_SMEM_STACK * PT_BLOCK];
     int2 *my_stack = s_stack + threadIdx.x;
     int2 deep_stack[PT_LBVH_STACK - WF_SMEM_STACK];
-#if !PT_PARITY
-    // the outlier list as merged primitives in the pair layout of brute_smem_prims (pt_kernels.cuh): at most 32 pairs
-    __shared__ float4 s_big[7 * (LBVH_BIG_MAX / 2)];
-    const int n_big_pairs = COUNT ? 0 : (sc.n_big_prims + 1) >> 1;
-    for (int j = threadIdx.x; j < n_big_pairs; j += PT_BLOCK) {
-        const int ia = 2 * j, ib = 2 * j + 1;
-        const bool hb = ib < sc.n_big_prims;
-        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        const float4 A0 = ldg4(sc.bq0 + ia), A1 = ldg4(sc.bq1 + ia), A2 = ldg4(sc.bq2 + ia);
-        const float4 B0 = hb ? ldg4(sc.bq0 + ib) : z, B1 = hb ? ldg4(sc.bq1 + ib) : z, B2 = hb ? ldg4(sc.bq2 + ib) : z;
-        const float2 sa = __ldg(sc.big_ab + ia), sb = hb ? __ldg(sc.big_ab + ib) : make_float2(1.0f, 0.0f);
-        s_big[7 * j + 0] = make_float4(A0.x, B0.x, A0.y, B0.y);
-        s_big[7 * j + 1] = make_float4(A0.z, B0.z, -A0.w, -B0.w);
-        s_big[7 * j + 2] = make_float4(-A1.x, -B1.x, -A1.y, -B1.y);
-        s_big[7 * j + 3] = make_float4(A1.z, B1.z, A1.w, B1.w);
-        s_big[7 * j + 4] = make_float4(A2.x, B2.x, A2.y, B2.y);
-        s_big[7 * j + 5] = make_float4(A2.z, B2.z, A2.w, B2.w);
-        s_big[7 * j + 6] = make_float4(-sa.x, -sb.x, -sa.y, -sb.y);
-    }
-    if (n_big_pairs > 0) __syncthreads();
-#endif
     int st = WF_FETCH, link = 0, sp = 0, path = 0;
     bool exhausted = count == 0;
     V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
@@ -268,14 +304,7 @@ __global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, 
                     ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
                     ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
                     nx = ix < 0.0f ? 1 : 0; ny = iy < 0.0f ? 1 : 0; nz = iz < 0.0f ? 1 : 0;
-                    best.t = PT_NO_HIT; best.tri = 0x7fffffff;
-#if !PT_PARITY
-                    if (n_big_pairs > 0) {                            // packed scan over the merged outliers, then primitive -> upload index
-                        brute_smem_prims<2>(s_big, n_big_pairs, P, D, best);
-                        if (best.t < PT_NO_HIT) best.tri = __ldg(sc.big_rep + best.tri);
-                    } else
-#endif
-                    lbvh_big_scan<COUNT>(sc, P, D, best, wk);
+                    best.t = r1.z; best.tri = __float_as_int(r1.w);        // the outlier scan ran where the ray was created (wf_big_scan)
                     sp = 0;
                     link = sc.bvh_root;
                     st = link >= 0 ? WF_NODE : WF_LEAF;
