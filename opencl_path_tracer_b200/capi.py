@@ -37,7 +37,8 @@ class Counters(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libptb200.so")
+    """libptb200.so next to this file; PTB200_LIB names another build of the same library (A/B experiments)."""
+    return os.environ.get("PTB200_LIB") or os.path.join(_HERE, "libptb200.so")
 
 
 def load_library(path=None):

@@ -323,7 +323,6 @@ __global__ void k_depth(int n, int leaf_size, const int2 *range, const int *pare
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(err, errcap, "lbvh: %s failed: %s", #x, cudaGetErrorString(e_)); return -1; } } while (0)
 
-template <typename T> cudaError_t dalloc(T **p, size_t count) { return cudaMalloc((void **)p, count * sizeof(T) + 16); }
 
 }  // namespace
 
@@ -347,11 +346,42 @@ void lbvh_free(Lbvh *b) {
     if (!b) return;
     if (b->bvh_tex) cudaDestroyTextureObject(b->bvh_tex);
     if (b->bvh4_tex) cudaDestroyTextureObject(b->bvh4_tex);
-    cudaFree(b->bvh); cudaFree(b->sq0); cudaFree(b->sq1); cudaFree(b->sq2); cudaFree(b->sf0); cudaFree(b->sf1); cudaFree(b->sf2); cudaFree(b->sorted_id);
-    cudaFree(b->bvh4); cudaFree(b->parent); cudaFree(b->flag4); cudaFree(b->id4);
-    cudaFree(b->range); cudaFree(b->child); cudaFree(b->leaf_lo); cudaFree(b->leaf_hi); cudaFree(b->node_lo); cudaFree(b->node_hi);
+    cudaFree(b->arena);
     memset(b, 0, sizeof(*b));
 }
+
+namespace {
+// bump allocator over the arena: every array 256-byte aligned; with base == nullptr it only measures
+struct Carver {
+    char *base;
+    size_t off;
+    template <typename T> T *take(size_t count) {
+        off = (off + 255) & ~(size_t)255;
+        T *p = base ? reinterpret_cast<T *>(base + off) : nullptr;
+        off += count * sizeof(T) + 16;
+        return p;
+    }
+};
+struct Scratch {
+    unsigned *bounds; unsigned long long *keys, *keys2; int *vals, *vals2, *pleaf, *arrivals, *stats;
+    void *sort_tmp, *scan_tmp;
+};
+// the layout is a function of the capacity alone, so the pointers stay put across rebuilds
+size_t lbvh_carve(Lbvh *b, Scratch &t, char *base, size_t cap, size_t sort_bytes, size_t scan_bytes) {
+    Carver c{base, 0};
+    b->bvh = c.take<float4>(4 * cap); b->bvh4 = c.take<float4>(8 * cap);
+    b->parent = c.take<int>(cap); b->flag4 = c.take<int>(cap); b->id4 = c.take<int>(cap + 1);
+    b->sq0 = c.take<float4>(cap); b->sq1 = c.take<float4>(cap); b->sq2 = c.take<float4>(cap);
+    b->sf0 = c.take<float4>(cap); b->sf1 = c.take<float4>(cap); b->sf2 = c.take<float4>(cap);
+    b->sorted_id = c.take<int>(cap);
+    b->range = c.take<int2>(cap); b->child = c.take<int2>(cap);
+    b->leaf_lo = c.take<float4>(cap); b->leaf_hi = c.take<float4>(cap); b->node_lo = c.take<float4>(cap); b->node_hi = c.take<float4>(cap);
+    t.bounds = c.take<unsigned>(8); t.keys = c.take<unsigned long long>(cap); t.keys2 = c.take<unsigned long long>(cap);
+    t.vals = c.take<int>(cap); t.vals2 = c.take<int>(cap); t.pleaf = c.take<int>(cap); t.arrivals = c.take<int>(cap); t.stats = c.take<int>(4);
+    t.sort_tmp = c.take<char>(sort_bytes); t.scan_tmp = c.take<char>(scan_bytes);
+    return c.off + 256;
+}
+}  // namespace
 
 int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
     // inflate every box by 2^-16 of the largest coordinate magnitude a ray can carry (scene or eye):
@@ -378,25 +408,37 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
 
 int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
                int n, int leaf_size, float big_frac, cudaStream_t st, char *err, size_t errcap) {
-    lbvh_free(b);
+    if (b->bvh_tex) cudaDestroyTextureObject(b->bvh_tex);
+    if (b->bvh4_tex) cudaDestroyTextureObject(b->bvh4_tex);
+    {   // forget the previous tree, keep the arena
+        void *arena = b->arena; const size_t arena_bytes = b->arena_bytes; const int cap = b->cap;
+        memset(b, 0, sizeof(*b));
+        b->arena = arena; b->arena_bytes = arena_bytes; b->cap = cap;
+    }
     b->n_tris = n;
     b->n_tree = n;
     b->n_big = 0;
     b->leaf_size = leaf_size < 1 ? 1 : (leaf_size > 8 ? 8 : leaf_size);
     if (n <= 0) { b->root = ~0; b->n_tris = 0; b->n_tree = 0; return 0; }
     if (n >= (1 << 28)) { snprintf(err, errcap, "lbvh: too many triangles (%d)", n); return -1; }
+    if (n > b->cap) { cudaFree(b->arena); b->arena = nullptr; b->arena_bytes = 0; b->cap = 0; }
+    const int cap = b->cap > 0 ? b->cap : n;
+    Scratch t{};
+    size_t sort_bytes = 0, scan_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (unsigned long long *)nullptr, (unsigned long long *)nullptr, (int *)nullptr, (int *)nullptr, cap, 0, 64, st));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int *)nullptr, (int *)nullptr, cap, st));
+    if (!b->arena) {
+        const size_t bytes = lbvh_carve(b, t, nullptr, (size_t)cap, sort_bytes, scan_bytes);
+        CK(cudaMalloc(&b->arena, bytes));
+        b->arena_bytes = bytes;
+        b->cap = cap;
+    }
+    lbvh_carve(b, t, (char *)b->arena, (size_t)cap, sort_bytes, scan_bytes);
+    unsigned *bounds = t.bounds; unsigned long long *keys = t.keys, *keys2 = t.keys2;
+    int *vals = t.vals, *vals2 = t.vals2, *pnode = b->parent, *pleaf = t.pleaf, *arrivals = t.arrivals, *stats = t.stats;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     CK(cudaEventRecord(e0, st));
-
-    unsigned *bounds; unsigned long long *keys, *keys2; int *vals, *vals2, *pnode, *pleaf, *arrivals, *stats;
-    CK(dalloc(&bounds, 8)); CK(dalloc(&keys, n)); CK(dalloc(&keys2, n)); CK(dalloc(&vals, n)); CK(dalloc(&vals2, n));
-    CK(dalloc(&b->parent, n)); CK(dalloc(&b->flag4, n)); CK(dalloc(&b->id4, n + 1)); pnode = b->parent;
-    CK(dalloc(&pleaf, n)); CK(dalloc(&arrivals, n)); CK(dalloc(&stats, 4));
-    CK(dalloc(&b->sq0, n)); CK(dalloc(&b->sq1, n)); CK(dalloc(&b->sq2, n)); CK(dalloc(&b->sorted_id, n));
-    CK(dalloc(&b->sf0, n)); CK(dalloc(&b->sf1, n)); CK(dalloc(&b->sf2, n));
-    CK(dalloc(&b->leaf_lo, n)); CK(dalloc(&b->leaf_hi, n)); CK(dalloc(&b->node_lo, n)); CK(dalloc(&b->node_hi, n));
-    CK(dalloc((int2 **)&b->range, n)); CK(dalloc((int2 **)&b->child, n)); CK(dalloc(&b->bvh, (size_t)4 * n));
 
     unsigned init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
     CK(cudaMemcpyAsync(bounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
@@ -418,11 +460,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     b->n_big = n_big;
     b->n_tree = n - n_big;
     const int m = b->n_tree;                                // triangles under the tree: Morton positions [0, m)
-    size_t tmp_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
-    void *tmp;
-    CK(cudaMalloc(&tmp, tmp_bytes + 16));
-    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
+    CK(cub::DeviceRadixSort::SortPairs(t.sort_tmp, sort_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
     k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, vals2, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi);
     CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
     b->launches += 1;
@@ -446,18 +484,12 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     if (b->root >= 0) {                              // 4-ary collapse: flags, compact ids, node storage
         k_flag4<<<grid, 256, 0, st>>>(m, b->leaf_size, (const int2 *)b->range, pnode, b->flag4);
         CK(cudaMemsetAsync(b->flag4 + (m - 1), 0, sizeof(int), st));
-        size_t scan_bytes = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, b->flag4, b->id4, m, st));
-        void *scan_tmp;
-        CK(cudaMalloc(&scan_tmp, scan_bytes + 16));
-        CK(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, b->flag4, b->id4, m, st));
+        CK(cub::DeviceScan::ExclusiveSum(t.scan_tmp, scan_bytes, b->flag4, b->id4, m, st));
         int total = 0;
         CK(cudaMemcpyAsync(&total, b->id4 + (m - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        cudaFree(scan_tmp);
         b->launches += 2;
-        b->n_nodes4 = total;
-        CK(dalloc(&b->bvh4, (size_t)8 * (total > 0 ? total : 1)));
+        b->n_nodes4 = total;                         // <= m - 1 < cap: the arena's 8 * cap float4 always hold them
     }
     if (lbvh_emit(b, 0.0f, st, err, errcap)) return -1;
     if (m >= 2 && (size_t)4 * m < ((size_t)1 << 27)) b->bvh_tex = linear_tex(b->bvh, (size_t)4 * m);
@@ -466,8 +498,6 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     CK(cudaEventSynchronize(e1));
     CK(cudaEventElapsedTime(&b->build_ms, e0, e1));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(pleaf); cudaFree(arrivals); cudaFree(stats); cudaFree(tmp);
     CK(cudaGetLastError());
     return 0;
 }

@@ -25,6 +25,11 @@ struct Lbvh {
     int n_tree, n_big;            // Morton positions [0, n_tree) are under the tree, [n_tree, n_tris) is the outlier list
     float max_abs, reach, eps, build_ms;
     unsigned long long launches;
+    // one device allocation holds every array above plus the build's scratch; it is kept across rebuilds (a re-upload of
+    // the same scene rebuilds the tree without a single cudaMalloc / cudaFree) and regrown only for more triangles
+    void *arena;
+    size_t arena_bytes;
+    int cap;                      // triangles the arena is laid out for
 };
 
 // q*: staged triangles in upload order (parity layout, holds the vertices); f*: the same triangles in the fast layout

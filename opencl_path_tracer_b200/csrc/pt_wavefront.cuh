@@ -257,8 +257,11 @@ enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 // predicated store, and ALL lanes that need a stack entry (no child hit, or a leaf just finished) share one pop block
 // that tries two entries per step and drops the culled ones — the first version branched three ways per lane here and
 // spent 47 % of its instructions at fewer than 12 active lanes (profiles/r01_wf_trace_v2.txt).
+#ifndef WF_MINB
+#define WF_MINB 8                 // resident blocks per SM the register allocation is held to
+#endif
 template <bool COUNT, bool WIDE>
-__global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor, const int3 tune) {
+__global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor, const int3 tune) {
     const SceneDev &sc = p.sc;
     const int lane = threadIdx.x & 31;
     const int count = *n_in;
