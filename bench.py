@@ -27,7 +27,14 @@ import numpy as np
 
 EMIT = print          # replaced by _QuietStdout.emit when run as a script
 # measured once under ncu (never inside a timed run): DRAM bytes of one launch of the dominant kernel, per workload
-NCU_DRAM_BYTES_PER_LAUNCH = {"cornell_1080p_1024spp_d4": 32.8e6}   # 8.35 MB read + 24.46 MB written
+NCU_DRAM_BYTES_PER_LAUNCH = {"cornell_1080p_1024spp_d4": 32.8e6,      # 8.35 MB read + 24.46 MB written
+                             "spheres100k_1080p_256spp_d4": 85.8e6}   # k_wf_trace, one iteration: 82.2 MB read + 3.6 MB written
+NCU_DRAM_SOURCE = {
+    "cornell_1080p_1024spp_d4": "dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, ncu --set full (profiles/r01_render_v7.txt); "
+                                "per launch, independent of spp: the per-pixel state is touched once",
+    "spheres100k_1080p_256spp_d4": "dram__bytes_read.sum + dram__bytes_write.sum of one k_wf_trace launch (one bounce of every path: 2.07 M rays), "
+                                   "ncu --set full (profiles/r01_wf_trace_v7.txt): the 64 B ray records and the queue; the 15 MB tree stays in L2",
+}
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -59,6 +66,9 @@ def parse():
     ap.add_argument("--split", default="spp", choices=["spp", "tile"],
                     help="N > 1: spp (weak scaling: every rank renders spp samples of every pixel, reduce(SUM)) or tile (strong scaling: "
                          "the frame's bands of 8 scanlines round-robin over the ranks with the reference's seeds, bitwise the 1-GPU image)")
+    ap.add_argument("--gather", default="nccl", choices=["nccl", "p2p"],
+                    help="--split tile: nccl = one reduce of the disjoint pixel sets per step; p2p = every rank's kernels store their pixels "
+                         "straight into rank 0's colors buffer over NVLink (CUDA IPC mapping), a barrier and no collective per step")
     ap.add_argument("--emulate-shard", type=int, default=0, metavar="N",
                     help="N = 1 GPU only, profiling aid: render just rank 0's share of an N-way tile split (what one GPU of --gpus N --split tile does)")
     ap.add_argument("--ref-spp", type=int, default=0, help="reference arm: samples per step (default: sized to a few seconds)")
@@ -217,6 +227,9 @@ def main():
     seeds_host = torch.from_numpy(host.minstd_rand0_seeds(W * H, seed_skip)).pin_memory()
     frame.rnds.copy_(seeds_host)
     frame.attach(scene)
+    p2p = tile and args.gather == "p2p"
+    if p2p:                                      # every rank's colors argument is rank 0's buffer
+        frame.h_colors = scene.buffer_colors = multigpu.share_root_colors(ptb, W, H)
     scene.upload_Triangles()
     scene.upload_Materials()
     scene.iterations = depth
@@ -237,6 +250,10 @@ def main():
 
     def step():
         scene.current_sample = 0
+        if p2p:
+            scene.render_spp(spp)
+            multigpu.finish_peer_gather(ptb)     # stream drained + barrier: rank 0 holds the frame
+            return
         if world > 1:
             frame.colors.zero_()
         scene.render_spp(spp)
@@ -357,10 +374,12 @@ def main():
         peak_tflops = sms * FP32_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
         per_gpu_rays_s = total_rays / world / (total_ms * 1e-3)
         achieved = f_ray * per_gpu_rays_s / 1e12
+        wavefront = accel_used == "lbvh" and args.pipeline != "megakernel"
+        kernel_name = ("k_wf_trace (wavefront closest-hit over the 4-ary LBVH; k_wf_shade is the other ~20 % of a step)" if wavefront
+                       else "k_render (fused gen_ray + trace_ray + accumulate)")
         roof = {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, "
-                "ncu --set full (profiles/r01_render_v7.txt); per launch, independent of spp: the per-pixel state is touched once",
-                "kernel": "k_render (fused gen_ray + trace_ray + accumulate)",
+                "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload), "traffic_source": NCU_DRAM_SOURCE.get(args.workload),
+                "kernel": kernel_name,
                 "peak_source": f"{sms} SMs x 128 FP32 lanes x 2 x {sm_max:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); the path has no dense contraction "
                                "and ~0 mandatory HBM traffic, so neither the hbm nor the tensor roofline bounds it (SURVEY 8d)",
                 "numerator": "algorithmic flops of the reference's closest-hit search for this scene (counting pass over the plain triangles); "
@@ -392,7 +411,9 @@ def main():
                        "scan_primitives": int(ptb.scan_prims()) if accel_used.startswith("brute") and args.math == "fast" else None,
                        "accel": accel_used, "math": args.math, "pipeline": args.pipeline,
                        "parallelism": "single GPU" if world == 1 else
-                       (f"tile-split x{world} (bands of 8 scanlines round-robin, reference seeds) + NCCL reduce of the disjoint pixel sets per step" if tile
+                       ((f"tile-split x{world} (bands of 8 scanlines round-robin, reference seeds), gather fused into the path kernel: every rank stores "
+                         "its pixels into rank 0's colors buffer over NVLink (CUDA IPC), barrier only" if p2p else
+                         f"tile-split x{world} (bands of 8 scanlines round-robin, reference seeds) + NCCL reduce of the disjoint pixel sets per step") if tile
                         else f"spp-split x{world} + NCCL reduce(SUM) of the accumulation buffer per step"),
                        "l2": "512 MB buffer written between timed steps (L2 flush)", "setup_s": setup_s,
                        "lbvh": ptb.accel_stats() if accel_used == "lbvh" else None},

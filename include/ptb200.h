@@ -82,6 +82,14 @@ int ptb_ingest_mesh(ptb_mem tris, size_t first_tri, const float *vertices, size_
 /* extensions for hosts that own device memory already (torch tensors, NCCL buffers) */
 ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes);  /* non-owning handle */
 void *ptb_device_ptr(ptb_mem m);
+/* Peer memory over NVLink (one process per GPU): the owner exports a ptb_alloc'ed buffer as a 64-byte CUDA IPC handle,
+ * a process on another GPU of the box imports it and binds it as a kernel argument like any other buffer.  Used by the
+ * tile split: every rank's path kernel stores its pixels' colors[] straight into rank 0's frame, so the
+ * gather rides on the kernel's own epilogue stores instead of a collective after it.  No equivalent in the reference
+ * (single device, main.cpp:496-506). */
+#define PTB_IPC_HANDLE_BYTES 64
+int ptb_ipc_export(ptb_mem m, void *handle_out /* PTB_IPC_HANDLE_BYTES */);
+ptb_mem ptb_ipc_import(const void *handle_in /* PTB_IPC_HANDLE_BYTES */, size_t bytes);   /* release with ptb_release */
 
 /* ---- kernels: replaces cl::Kernel::setArg (main.cpp:638-640, 648-660) and
  *      enqueueNDRangeKernel / finish (main.cpp:642,674,675,678,680).

@@ -16,7 +16,7 @@ PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO = 0, 1, 2
 SYMBOLS = [
     "ptb_init", "ptb_shutdown", "ptb_device_string", "ptb_device_compute_units", "ptb_backend_name",
     "ptb_alloc", "ptb_alloc_image", "ptb_retain", "ptb_release", "ptb_write", "ptb_read", "ptb_mem_size", "ptb_ingest_mesh",
-    "ptb_wrap_device", "ptb_device_ptr", "ptb_kernel_id", "ptb_set_arg", "ptb_set_arg_mem", "ptb_launch",
+    "ptb_wrap_device", "ptb_device_ptr", "ptb_ipc_export", "ptb_ipc_import", "ptb_kernel_id", "ptb_set_arg", "ptb_set_arg_mem", "ptb_launch",
     "ptb_finish", "ptb_last_error", "ptb_clear_error", "ptb_set_accel", "ptb_set_math", "ptb_set_pipeline",
     "ptb_set_fuse_gen", "ptb_set_lbvh_leaf", "ptb_set_merge_prims", "ptb_set_parity_filter", "ptb_scan_prims", "ptb_get_accel", "ptb_build_accel", "ptb_render",
     "ptb_set_pixel_shard", "ptb_set_accumulate_sum", "ptb_resolve_sum", "ptb_set_count_work", "ptb_get_counters",
@@ -57,6 +57,7 @@ def load_library(path=None):
         "ptb_write": (i, [u64, sz, sz, vp]), "ptb_read": (i, [u64, sz, sz, vp]), "ptb_mem_size": (sz, [u64]), "ptb_closest_hit": (i, [u64, sz, u64]),
         "ptb_ingest_mesh": (i, [u64, sz, vp, sz, vp, vp, sz, vp, vp, C.c_float, C.c_float, i]),
         "ptb_wrap_device": (u64, [vp, sz]), "ptb_device_ptr": (vp, [u64]),
+        "ptb_ipc_export": (i, [u64, vp]), "ptb_ipc_import": (u64, [vp, sz]),
         "ptb_kernel_id": (i, [cp]), "ptb_set_arg": (i, [i, i, sz, vp]), "ptb_set_arg_mem": (i, [i, i, u64]),
         "ptb_launch": (i, [i, sz, sz]), "ptb_finish": (i, []), "ptb_last_error": (cp, []), "ptb_clear_error": (None, []),
         "ptb_set_accel": (i, [i]), "ptb_set_math": (i, [i]), "ptb_set_pipeline": (i, [i]), "ptb_set_fuse_gen": (i, [i]),
@@ -179,6 +180,20 @@ class Ptb:
 
     def device_ptr(self, h):
         return self.lib.ptb_device_ptr(h)
+
+    def ipc_export(self, h):
+        """64-byte CUDA IPC handle of a ptb.alloc'ed buffer (bytes), for a process on another GPU of the box."""
+        buf = C.create_string_buffer(64)
+        self._ck(self.lib.ptb_ipc_export(h, buf), "ptb_ipc_export")
+        return buf.raw
+
+    def ipc_import(self, handle_bytes, nbytes):
+        """Map another process's exported buffer; the returned handle binds as a kernel argument like a local one."""
+        buf = C.create_string_buffer(bytes(handle_bytes), 64)
+        h = self.lib.ptb_ipc_import(buf, nbytes)
+        if not h:
+            raise PtbError("ptb_ipc_import: " + self.last_error())
+        return h
 
     # -- kernels
     def set_arg(self, kernel, index, value):

@@ -194,7 +194,10 @@ __global__ void __launch_bounds__(256) k_wf_init(const RenderParams p, const int
 
 // ---------------------------------------------------------------- shade: one thread per queued path
 // q_in/n_in: this iteration's queue; survivors go to q_out/n_out (zeroed by the host before the launch)
-__global__ void __launch_bounds__(256) k_wf_shade(const RenderParams p, const int *q_in, const int *n_in, int *q_out, int *n_out) {
+#ifndef WF_SHADE_MINB
+#define WF_SHADE_MINB 4            // 64 registers: 32 resident warps per SM against the four dependent loads of a path step
+#endif
+__global__ void __launch_bounds__(256, WF_SHADE_MINB) k_wf_shade(const RenderParams p, const int *q_in, const int *n_in, int *q_out, int *n_out) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int count = *n_in;
     Work wk = {0, 0, 0, 0, 0, 0, 0};

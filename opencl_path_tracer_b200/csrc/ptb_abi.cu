@@ -31,6 +31,7 @@ struct MemObj {
     size_t bytes = 0;
     int refs = 1;
     bool owned = true;
+    bool ipc = false;                 // mapped from another process (ptb_ipc_import): closed, not freed, on release
     bool image = false;
     int w = 0, h = 0;
     unsigned long long version = 0;   // bumped by every write: invalidates staged copies
@@ -578,6 +579,7 @@ int ptb_release(ptb_mem h) {
         if (G.inited) {
             if (G.pending.active && (G.pending.rays == h || G.pending.rnds == h)) G.pending.active = false;
             if (m->owned) { cudaStreamSynchronize(G.stream); cudaFree(m->dptr); }
+            else if (m->ipc) { cudaStreamSynchronize(G.stream); cudaIpcCloseMemHandle(m->dptr); }
         }
         if (G.staged.tris_handle == h) G.staged.tris_handle = 0;
         G.mems.erase(h);
@@ -663,6 +665,35 @@ ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes) {
     m.dptr = device_ptr;
     m.bytes = bytes;
     m.owned = false;
+    ptb_mem h = G.next++;
+    G.mems[h] = m;
+    return h;
+}
+int ptb_ipc_export(ptb_mem h, void *handle_out) {
+    NEED_INIT();
+    MemObj *m = find(h);
+    if (!m) return fail(PTB_ERR_INVALID_MEM, "ptb_ipc_export: bad handle");
+    if (!handle_out) return fail(PTB_ERR_INVALID_VALUE, "ptb_ipc_export: null output");
+    if (!m->owned || m->image) return fail(PTB_ERR_INVALID_VALUE, "ptb_ipc_export: only ptb_alloc'ed buffers (a whole device allocation) can be exported");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PTB_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t ipc;
+    CUDA_OK(cudaIpcGetMemHandle(&ipc, m->dptr));
+    memcpy(handle_out, &ipc, sizeof ipc);
+    return PTB_SUCCESS;
+}
+ptb_mem ptb_ipc_import(const void *handle_in, size_t bytes) {
+    if (!G.inited && ptb_init(-1)) return 0;
+    if (!handle_in || bytes == 0) { fail(PTB_ERR_INVALID_VALUE, "ptb_ipc_import: null handle or zero size"); return 0; }
+    cudaIpcMemHandle_t ipc;
+    memcpy(&ipc, handle_in, sizeof ipc);
+    void *ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, ipc, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess || !ptr) { cudaGetLastError(); fail(PTB_ERR_DEVICE, "ptb_ipc_import: cudaIpcOpenMemHandle: %s", cudaGetErrorString(e)); return 0; }
+    MemObj m;
+    m.dptr = ptr;
+    m.bytes = bytes;
+    m.owned = false;
+    m.ipc = true;
     ptb_mem h = G.next++;
     G.mems[h] = m;
     return h;

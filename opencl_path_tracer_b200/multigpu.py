@@ -12,6 +12,11 @@ exactly one exchange step per render:
   reference's per-pixel seeds, then the disjoint pixel sets are summed (every pixel is non-zero on
   exactly one rank) — bitwise identical to the 1-GPU image.
 
+* **tile-split with a peer-memory gather** (`share_root_colors`) — rank 0 allocates the frame's ``colors`` buffer, exports
+  it as a CUDA IPC handle, and every other rank binds the imported mapping as ITS ``colors`` kernel argument: the path
+  kernel's own end-of-pixel store lands in rank 0's HBM over NVLink, pixel by pixel as paths finish, so the gather is
+  fused into the kernel's epilogue and only a barrier (no data) follows the render.  Same bits as the all-reduce merge.
+
 The collective runs on whatever backend the process group has (NCCL on the GPU box, gloo in the CPU
 tests); only the render call needs the CUDA library.
 """
@@ -54,6 +59,51 @@ def merge_tile_split(local_colors, group=None):
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(local_colors, op=dist.ReduceOp.SUM, group=group)
     return local_colors
+
+
+def share_root_colors(ptb, width, height, group=None, root=0):
+    """Peer-memory gather of the tile split: returns a ptb handle to bind as ``colors`` (``scene.buffer_colors``).  On
+    ``root`` it is a fresh ptb.alloc'ed W*H float4 buffer; on every other rank it is that same memory mapped through
+    CUDA IPC (ptb_ipc_export / ptb_ipc_import), so the rank's kernels write their pixels straight into the root's frame.
+    The 64-byte handle travels through the process group (control plane only)."""
+    nbytes = width * height * 16
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return ptb.alloc(nbytes)
+    payload = [None]
+    h = None
+    if rank == root:
+        h = ptb.alloc(nbytes)
+        payload = [ptb.ipc_export(h)]
+    dist.broadcast_object_list(payload, src=root, group=group)
+    if rank != root:
+        h = ptb.ipc_import(payload[0], nbytes)
+    return h
+
+
+def finish_peer_gather(ptb, group=None):
+    """After a render into shared colors: every rank's stores are complete once its stream has drained; the barrier tells
+    the root that all of them have.  No pixel data moves here."""
+    ptb.finish()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+
+
+def render_progressive(scene, ptb, total_spp, refresh_spp, on_refresh=None, group=None):
+    """Progressive tile-split render with a refresh cadence (BASELINE configs[4]; the reference refreshes its window every
+    sample, main.cpp:670-681): ``refresh_spp`` samples per launch into the shared colors buffer (share_root_colors), then
+    drain + barrier, then ``on_refresh(samples_done)`` on every rank (the root resolves / writes the image there — its
+    buffer holds the whole frame's running mean).  The launches continue each pixel's sample index and RNG stream, so
+    the final image is bitwise the one-launch, one-GPU render of ``total_spp`` samples."""
+    done = 0
+    while done < total_spp:
+        n = min(refresh_spp, total_spp - done)
+        scene.render_spp(n)
+        finish_peer_gather(ptb, group)
+        done += n
+        if on_refresh is not None:
+            on_refresh(done)
+    return done
 
 
 class DeviceFrame:

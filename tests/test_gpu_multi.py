@@ -3,6 +3,9 @@ code runs world-size 2 over gloo in tests/test_multigpu_cpu.py.
 
 * tile-split: the union of the two ranks' pixel shards after the SUM all-reduce is BITWISE the 1-GPU image (parity
   flavour, reference seeds).
+* tile-split with the peer-memory gather (multigpu.share_root_colors): rank 1's kernels store into rank 0's colors
+  buffer through a CUDA IPC mapping; after a barrier rank 0's buffer is BITWISE the 1-GPU image, also across three
+  progressive launches (the later ones read the running mean back through the mapping).
 * spp-split: rank r renders spp samples of every pixel from seed offset r*W*H into a SUM buffer, one NCCL reduce to rank
   0, resolve by the total: rank 0's own half is bitwise the 1-GPU render of spp samples, and the merged image agrees
   with a 1-GPU render of 2*spp samples to Monte-Carlo accuracy (different random numbers: RMSE bound, not equality).
@@ -67,6 +70,18 @@ def _worker(rank, world, port, out_dir):
     multigpu.merge_tile_split(frame.colors)
     torch.cuda.synchronize()
     tile = frame.colors.cpu().numpy().reshape(H, W, 4)
+
+    # ---- the same tile split with the gather fused into the kernels' own stores: every rank's colors argument IS rank 0's
+    # buffer (CUDA IPC mapping over NVLink); after the barrier rank 0 holds the whole frame, no collective moved a pixel
+    s1 = _scene(ptb)
+    shared = multigpu.share_root_colors(ptb, W, H)
+    s1.buffer_colors = shared
+    refreshes = []                                # progressive: 3 launches of 6/6/4 samples, the running mean is read back through the mapping
+    multigpu.render_progressive(s1, ptb, SPP, 6, on_refresh=refreshes.append)
+    assert refreshes == [6, 12, 16]
+    peer = ptb.read(shared, np.float32, W * H * 4).reshape(H, W, 4) if rank == 0 else np.zeros((H, W, 4), np.float32)
+    dist.barrier()
+    ptb.release(shared)
     ptb.set_pixel_shard(0, 1, 1)
 
     # ---- spp split: my own seed set, SUM buffer, one reduce to rank 0, resolve by the total
@@ -85,7 +100,7 @@ def _worker(rank, world, port, out_dir):
         ptb.finish()
     merged = frame2.colors.cpu().numpy().reshape(H, W, 4)
     ptb.set_accumulate_sum(0)
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), tile=tile, mine=mine, merged=merged)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), tile=tile, mine=mine, merged=merged, peer=peer)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -111,6 +126,7 @@ def test_two_gpus_tile_split_is_bitwise_and_spp_split_converges(ptb, tmp_path):
     two = s.download_colors().copy()
     ptb.finish()
     assert (bits(r0["tile"]) == bits(one)).all() and (bits(r1["tile"]) == bits(one)).all()
+    assert (bits(r0["peer"]) == bits(one)).all()           # peer-memory gather, three progressive launches: the same bits on rank 0
     # rank 0's SUM buffer / SPP is the 1-GPU mean up to the rounding of sum-vs-running-mean
     assert np.abs(r0["mine"][..., :3] / SPP - one[..., :3]).max() <= 2e-5 * max(1.0, float(one[..., :3].max()))
     # the merged image is a 2*SPP estimate from different random numbers: same expectation, Monte-Carlo distance
