@@ -126,6 +126,9 @@ enum {
 int ptb_set_accel(int accel);
 int ptb_set_math(int math);
 int ptb_set_pipeline(int pipe);
+/* wavefront pipeline: number of interleaved sub-wavefronts (independent ray queues on separate streams that fill each
+ * other's trace tails), 1..4, default 2 (env PTB_WF_SUBS).  The image does not depend on it. */
+int ptb_set_wf_subs(int n);
 /* The reference enqueues gen_ray then trace_ray for every sample (main.cpp:683-687).  With fusion on
  * (the default) a gen_ray launch is deferred and folded into the trace_ray launch that follows it on
  * the same rays/rnds buffers, so the primary rays never travel through rays[] (it is scratch in the

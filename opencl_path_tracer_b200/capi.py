@@ -17,7 +17,7 @@ SYMBOLS = [
     "ptb_init", "ptb_shutdown", "ptb_device_string", "ptb_device_compute_units", "ptb_backend_name",
     "ptb_alloc", "ptb_alloc_image", "ptb_retain", "ptb_release", "ptb_write", "ptb_read", "ptb_mem_size", "ptb_ingest_mesh",
     "ptb_wrap_device", "ptb_device_ptr", "ptb_ipc_export", "ptb_ipc_import", "ptb_kernel_id", "ptb_set_arg", "ptb_set_arg_mem", "ptb_launch",
-    "ptb_finish", "ptb_last_error", "ptb_clear_error", "ptb_set_accel", "ptb_set_math", "ptb_set_pipeline",
+    "ptb_finish", "ptb_last_error", "ptb_clear_error", "ptb_set_accel", "ptb_set_math", "ptb_set_pipeline", "ptb_set_wf_subs",
     "ptb_set_fuse_gen", "ptb_set_lbvh_leaf", "ptb_set_merge_prims", "ptb_set_parity_filter", "ptb_scan_prims", "ptb_get_accel", "ptb_build_accel", "ptb_render",
     "ptb_set_pixel_shard", "ptb_set_accumulate_sum", "ptb_resolve_sum", "ptb_set_count_work", "ptb_get_counters",
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
@@ -60,7 +60,7 @@ def load_library(path=None):
         "ptb_ipc_export": (i, [u64, vp]), "ptb_ipc_import": (u64, [vp, sz]),
         "ptb_kernel_id": (i, [cp]), "ptb_set_arg": (i, [i, i, sz, vp]), "ptb_set_arg_mem": (i, [i, i, u64]),
         "ptb_launch": (i, [i, sz, sz]), "ptb_finish": (i, []), "ptb_last_error": (cp, []), "ptb_clear_error": (None, []),
-        "ptb_set_accel": (i, [i]), "ptb_set_math": (i, [i]), "ptb_set_pipeline": (i, [i]), "ptb_set_fuse_gen": (i, [i]),
+        "ptb_set_accel": (i, [i]), "ptb_set_math": (i, [i]), "ptb_set_pipeline": (i, [i]), "ptb_set_wf_subs": (i, [i]), "ptb_set_fuse_gen": (i, [i]),
         "ptb_set_lbvh_leaf": (i, [i]), "ptb_set_merge_prims": (i, [i]), "ptb_set_parity_filter": (i, [i]), "ptb_scan_prims": (i, []), "ptb_get_accel": (i, []), "ptb_build_accel": (i, []), "ptb_render": (i, [i]),
         "ptb_set_pixel_shard": (i, [i, i, i]), "ptb_set_accumulate_sum": (i, [i]), "ptb_resolve_sum": (i, [u64, i]),
         "ptb_set_count_work": (i, [i]), "ptb_get_counters": (i, [C.POINTER(Counters)]), "ptb_reset_counters": (i, []),
@@ -222,6 +222,7 @@ class Ptb:
     def set_accel(self, a): self._ck(self.lib.ptb_set_accel(a), "ptb_set_accel")
     def set_math(self, m): self._ck(self.lib.ptb_set_math(m), "ptb_set_math")
     def set_pipeline(self, p): self._ck(self.lib.ptb_set_pipeline(p), "ptb_set_pipeline")
+    def set_wf_subs(self, n): self._ck(self.lib.ptb_set_wf_subs(n), "ptb_set_wf_subs")
     def set_fuse_gen(self, on): self._ck(self.lib.ptb_set_fuse_gen(int(on)), "ptb_set_fuse_gen")
     def set_lbvh_leaf(self, n): self._ck(self.lib.ptb_set_lbvh_leaf(n), "ptb_set_lbvh_leaf")
     def set_merge_prims(self, on): self._ck(self.lib.ptb_set_merge_prims(int(on)), "ptb_set_merge_prims")

@@ -70,6 +70,7 @@ struct RenderParams {
     int sum_mode;                 // 1: colors += sample (spp-split), 0: running mean (prog.cl:379)
     int accel;                    // PT_ACCEL_*
     int count_work;               // 1: also count box / triangle tests
+    int wf_subs;                  // wavefront: interleaved sub-wavefronts on separate streams (1..4; 0 = default 2)
     int wf_sort;                  // wavefront: group each shade block's surviving rays by direction octant in the next queue
     int parity_filter;            // parity flavour, brute force: conservative FFMA2 pre-filter in front of the exact test (pt_kernels.cuh)
     int rng_nonneg;               // 1: every RNG state of this launch was verified to lie in [0, 2^31) (pt_rand_nonneg)

@@ -260,6 +260,16 @@ enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 // predicated store, and ALL lanes that need a stack entry (no child hit, or a leaf just finished) share one pop block
 // that tries two entries per step and drops the culled ones — the first version branched three ways per lane here and
 // spent 47 % of its instructions at fewer than 12 active lanes (profiles/r01_wf_trace_v2.txt).
+// WF_POSTPONE: a lane that reaches a leaf while it holds no postponed one parks the leaf link in `pend` and keeps
+// traversing (its next stack entry) instead of idling until enough lanes want a leaf step; the leaf step then tests the
+// postponed and the current leaf of EVERY lane that has one.  The extra node visits are speculative (they run in slots
+// the lane would have idled through, and anything they push is culled at pop once the leaf has shrunk best.t); the
+// result cannot change: every leaf whose box passed is still tested before the ray finishes.
+// MEASURED (scripts/wf_ab.sh): 3.44 vs 3.48 Grays/s (104 k), 3.12 vs 3.15 (1 M) — box tests per ray +4 %, no time won:
+// the lanes the leaf step gains are lost again to the speculative visits.  Off by default, kept as the experiment.
+#ifndef WF_POSTPONE
+#define WF_POSTPONE 0
+#endif
 #ifndef WF_MINB
 #define WF_MINB 8                 // resident blocks per SM the register allocation is held to
 #endif
@@ -273,6 +283,7 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
     int2 *my_stack = s_stack + threadIdx.x;
     int2 deep_stack[PT_LBVH_STACK - WF_SMEM_STACK];
     int st = WF_FETCH, link = 0, sp = 0, path = 0;
+    int pend = 0;                                        // postponed leaf link (< 0), 0 = none
     bool exhausted = count == 0;
     V3 P = v3(0.0f, 0.0f, 0.0f), D = v3(0.0f, 0.0f, 1.0f);
     Closest best; best.t = PT_NO_HIT; best.tri = 0x7fffffff;
@@ -312,6 +323,7 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     nx = ix < 0.0f ? 1 : 0; ny = iy < 0.0f ? 1 : 0; nz = iz < 0.0f ? 1 : 0;
                     best.t = r1.z; best.tri = __float_as_int(r1.w);        // the outlier scan ran where the ray was created (wf_big_scan)
                     sp = 0;
+                    pend = 0;
                     link = sc.bvh_root;
                     st = link >= 0 ? WF_NODE : WF_LEAF;
                 } else {
@@ -328,11 +340,15 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     for (int attempt = 0; attempt < 2; ++attempt) {
                         if (st == WF_POP) {
                             if (sp == 0) {
-                                WF_FINISH();
+                                if (WF_POSTPONE && pend != 0) { link = 0; st = WF_LEAF; }     // only the postponed leaf is left
+                                else WF_FINISH();
                             } else {
                                 --sp;
                                 const int2 e = sp < WF_SMEM_STACK ? my_stack[sp * PT_BLOCK] : deep_stack[sp - WF_SMEM_STACK];
-                                if (__int_as_float(e.y) <= best.t) { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
+                                if (__int_as_float(e.y) <= best.t) {
+                                    if (WF_POSTPONE && e.x < 0 && pend == 0) pend = e.x;      // park it, keep popping
+                                    else { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
+                                }
                             }
                         }
                     }
@@ -371,8 +387,8 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     if (d3 < PT_NO_HIT) WF_PUSH(k3, d3);
                     if (d2 < PT_NO_HIT) WF_PUSH(k2, d2);
                     if (d1 < PT_NO_HIT) WF_PUSH(k1, d1);
-                    link = k0;
-                    st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
+                    if (WF_POSTPONE && d0 < PT_NO_HIT && k0 < 0 && pend == 0) { pend = k0; st = WF_POP; }
+                    else { link = k0; st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP; }
                 }
                 if (!WIDE && st == WF_NODE) {
                     const float4 *nd = sc.bvh + 4 * (size_t)link;
@@ -399,17 +415,19 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     const bool right_first = hr & (!hl | (r0 < l0));          // both hit: the nearer entry first, left on ties
                     const int near_link = right_first ? lr : ll, far_link = right_first ? ll : lr;
                     if (hl & hr) WF_PUSH(far_link, right_first ? l0e : r0e);
-                    link = near_link;
-                    st = (hl | hr) ? (near_link >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
+                    if (WF_POSTPONE && (hl | hr) && near_link < 0 && pend == 0) { pend = near_link; st = WF_POP; }
+                    else { link = near_link; st = (hl | hr) ? (near_link >= 0 ? WF_NODE : WF_LEAF) : WF_POP; }
                 }
             }
         } else {
             // ------------------------------------------------------------ LEAF step
-            if (st == WF_LEAF) {
-                const int enc = ~link;
-                const int first = enc >> 3, cnt = (enc & 7) + 1;
+            // every lane with a leaf to test takes part: the postponed one first, then the one it is blocked on
+            const int la = pend, lb = (st == WF_LEAF && link < 0) ? link : 0;
+            if ((la | lb) < 0) {
+                const int first_a = (~la) >> 3, cnt_a = la < 0 ? ((~la) & 7) + 1 : 0;
+                const int first_b = (~lb) >> 3, cnt = cnt_a + (lb < 0 ? ((~lb) & 7) + 1 : 0);
                 for (int k = 0; k < cnt; ++k) {
-                    const int pos = first + k;
+                    const int pos = k < cnt_a ? first_a + k : first_b + (k - cnt_a);
                     float t;
                     const bool acc_ = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
                     if (acc_ & (t > 0.0f) & (t <= best.t)) {
@@ -417,8 +435,9 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                         if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
                     }
                 }
-                st = WF_POP;
+                pend = 0;
             }
+            if (st == WF_LEAF) st = WF_POP;
         }
     }
 #undef WF_PUSH
@@ -457,7 +476,7 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     const int n = p.W * p.H;
     int launches = 0;
     WfStreams &ws = wf_streams();
-    static const int want_subs = getenv("PTB_WF_SUBS") ? atoi(getenv("PTB_WF_SUBS")) : 2;
+    const int want_subs = p.wf_subs > 0 ? p.wf_subs : 2;
     const int init_blocks = (n + 255) / 256;
     int subs = ws.ok ? (want_subs < 1 ? 1 : want_subs > WF_SUBS_MAX ? WF_SUBS_MAX : want_subs) : 1;
     if (subs > init_blocks) subs = init_blocks > 0 ? init_blocks : 1;

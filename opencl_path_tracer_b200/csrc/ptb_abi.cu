@@ -96,6 +96,7 @@ struct State {
     int lbvh_leaf = 4;
     int merge_prims = 1;
     int parity_filter = 1;
+    int wf_subs = 2;                   // PTB_WF_SUBS / ptb_set_wf_subs: sub-wavefronts of the wavefront pipeline (pt_wavefront.cuh)
     int wf_sort = 0;                   // PTB_WF_SORT=1: wavefront queues grouped by direction octant (measured slower)
     float lbvh_big = 0.25f;            // triangles spanning more than this fraction of the scene stay out of the tree (PTB_LBVH_BIG, 0 = off)
     int tex_nodes = 1;                 // node fetches through the texture pipe (PTB_TEX_NODES=0: LSU)
@@ -352,6 +353,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.sc.fq0 = s.f0; p.sc.fq1 = s.f1; p.sc.fq2 = s.f2;
     p.parity_filter = G.parity_filter;
     p.wf_sort = G.wf_sort;
+    p.wf_subs = G.wf_subs;
     if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
         rc = ensure_prims();
         if (rc) return rc;
@@ -494,6 +496,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_MERGE_PRIMS"))) G.merge_prims = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_PARITY_FILTER"))) G.parity_filter = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_WF_SORT"))) G.wf_sort = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_WF_SUBS"))) G.wf_subs = atoi(env) < 1 ? 1 : (atoi(env) > 4 ? 4 : atoi(env));
     if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
@@ -801,6 +804,11 @@ int ptb_set_math(int math) {
 int ptb_set_pipeline(int pipe) {
     if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT && pipe != PTB_PIPE_AUTO) return PTB_ERR_INVALID_VALUE;
     G.pipe = pipe;
+    return PTB_SUCCESS;
+}
+int ptb_set_wf_subs(int n) {
+    if (n < 1 || n > 4) return PTB_ERR_INVALID_VALUE;
+    G.wf_subs = n;
     return PTB_SUCCESS;
 }
 int ptb_set_fuse_gen(int on) {

@@ -174,3 +174,55 @@ def test_c3_lbvh_pipelines_agree_bitwise_at_1080p(ptb):
         release(s)
     assert (bits(out[0][0]) == bits(out[1][0])).all() and (out[0][1] == out[1][1]).all()
     assert out[0][0][..., :3].mean() > 0
+
+
+def _render_lbvh(ptb, d, spp, w=640, h=360):
+    s = host.Scene(ptb)
+    s.build_trees = False
+    s.init_Scene(w, h)
+    scenes.populate(s, d)
+    s.upload_Triangles(); s.upload_Materials()
+    s.iterations = DEPTH
+    cam = host.camera_at(w, h, d["fov"], d.get("yaw", 0), d.get("pitch", 0), d["eye"])
+    s._camera = lambda cam=cam: cam
+    s.render_spp(spp)
+    out = (s.download_colors().copy(), s.download_rnds().copy())
+    release(s)
+    return out
+
+
+def test_wavefront_image_does_not_depend_on_the_number_of_sub_wavefronts(ptb):
+    """The wavefront deals the frame's paths to 1..4 independent queues on separate streams (ptb_set_wf_subs); paths never
+    move between them and a pixel's samples stay sequential, so colours and RNG states are the same bits for every count,
+    in both flavours, at a frame size that is not a multiple of the 256-pixel dealing unit."""
+    d = scenes.describe("spheres100k")
+    try:
+        for math in (capi.MATH_PARITY, capi.MATH_FAST):
+            ptb.set_accel(capi.ACCEL_LBVH); ptb.set_math(math); ptb.set_pipeline(capi.PIPE_WAVEFRONT)
+            outs = []
+            for subs in (1, 2, 3, 4):
+                ptb.set_wf_subs(subs)
+                outs.append(_render_lbvh(ptb, d, 3, w=611, h=173))
+            for c, r in outs[1:]:
+                assert (bits(c) == bits(outs[0][0])).all() and (r == outs[0][1]).all()
+            assert outs[0][0][..., :3].mean() > 0
+    finally:
+        ptb.set_wf_subs(2)
+        ptb.set_math(capi.MATH_FAST)
+
+
+def test_lbvh_arena_survives_bigger_and_smaller_scenes(ptb):
+    """The LBVH lives in one arena that is kept across rebuilds and regrown only for more triangles (lbvh.cu): rendering
+    the 104 k-triangle scene, then the 1 M-triangle one (regrow), then the 104 k one again (reuse of the larger arena, no
+    allocation) must give the first image back bit for bit."""
+    small, big = scenes.describe("spheres100k"), scenes.describe("grid1m")
+    ptb.set_accel(capi.ACCEL_LBVH); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(capi.PIPE_WAVEFRONT)
+    try:
+        a = _render_lbvh(ptb, small, 2, w=320, h=180)
+        b = _render_lbvh(ptb, big, 1, w=320, h=180)
+        c = _render_lbvh(ptb, small, 2, w=320, h=180)
+        assert (bits(a[0]) == bits(c[0])).all() and (a[1] == c[1]).all()
+        assert b[0][..., :3].mean() > 0 and np.isfinite(b[0][..., :3]).all()
+        assert ptb.accel_stats()["tris"] == len(small["tri_mat"])          # the tree in place is the small scene's again
+    finally:
+        ptb.set_math(capi.MATH_FAST)
