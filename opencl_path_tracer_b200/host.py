@@ -476,6 +476,9 @@ class Scene:
     def save_pfm(self, path):
         write_pfm(path, self.download_colors()[..., :3])
 
+    def save_exr(self, path):
+        write_exr(path, self.download_colors()[..., :3])
+
 
 def write_ppm(path, rgba8):
     """binary PPM (P6) from an (H, W, 3|4) uint8 image whose first row is the TOP of the picture"""
@@ -492,6 +495,37 @@ def write_pfm(path, rgb):
     with open(path, "wb") as f:
         f.write(b"PF\n%d %d\n-1.0\n" % (img.shape[1], img.shape[0]))
         f.write(img.tobytes())
+
+
+def write_exr(path, rgb):
+    """OpenEXR 2 scanline file, three 32-bit float channels, no compression, from an (H, W, 3) float32 image whose first
+    row is the BOTTOM of the picture (the reference's convention, prog.cl:86-88; EXR's y = 0 is the top, so rows are
+    flipped).  Linear radiance as accumulated — what the reference could only show tone-mapped in its window."""
+    import struct
+    img = np.asarray(rgb, dtype="<f4")[::-1, :, :3]
+    h, w = img.shape[:2]
+
+    def attr(name, typ, payload):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(payload)) + payload
+
+    chlist = b"".join(c + b"\0" + struct.pack("<iBxxxii", 2, 0, 1, 1) for c in (b"B", b"G", b"R")) + b"\0"   # FLOAT, sampling 1 x 1
+    box = struct.pack("<iiii", 0, 0, w - 1, h - 1)
+    header = (struct.pack("<ii", 20000630, 2)
+              + attr("channels", "chlist", chlist) + attr("compression", "compression", b"\0")
+              + attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box)
+              + attr("lineOrder", "lineOrder", b"\0") + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0))
+              + attr("screenWindowCenter", "v2f", struct.pack("<ff", 0.0, 0.0))
+              + attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
+    row_bytes = 3 * w * 4
+    first = len(header) + 8 * h
+    offsets = (first + (8 + row_bytes) * np.arange(h, dtype=np.uint64)).astype("<u8")
+    planes = np.ascontiguousarray(img[:, :, ::-1].transpose(0, 2, 1))        # per scanline: all B, all G, all R
+    with open(path, "wb") as f:
+        f.write(header)
+        f.write(offsets.tobytes())
+        for y in range(h):
+            f.write(struct.pack("<ii", y, row_bytes))
+            f.write(planes[y].tobytes())
 
 
 # ---------------------------------------------------------------- dumps of the kernel-argument surface

@@ -96,3 +96,49 @@ def test_image_writers(tmp_path):
     host.write_pfm(tmp_path / "a.pfm", rgb)
     raw = (tmp_path / "a.pfm").read_bytes()
     assert raw.startswith(b"PF\n3 2\n-1.0\n") and np.frombuffer(raw[len(b"PF\n3 2\n-1.0\n"):], dtype="<f4").tolist() == rgb.ravel().tolist()
+
+
+def _read_exr(path):
+    """minimal reader of what host.write_exr writes (scanline, uncompressed, FLOAT channels): returns {name: (H, W)}"""
+    import struct
+    raw = open(path, "rb").read()
+    assert struct.unpack_from("<ii", raw, 0) == (20000630, 2)
+    off, attrs = 8, {}
+    while raw[off] != 0:
+        e = raw.index(b"\0", off); name = raw[off:e].decode(); off = e + 1
+        e = raw.index(b"\0", off); typ = raw[off:e].decode(); off = e + 1
+        (size,) = struct.unpack_from("<i", raw, off); off += 4
+        attrs[name] = (typ, raw[off:off + size]); off += size
+    off += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    x0, y0, x1, y1 = struct.unpack("<iiii", attrs["dataWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    names, c = [], attrs["channels"][1]
+    i = 0
+    while c[i] != 0:
+        e = c.index(b"\0", i); names.append(c[i:e].decode())
+        ptype, plin, xs, ys = struct.unpack_from("<iBxxxii", c, e + 1)
+        assert (ptype, xs, ys) == (2, 1, 1)
+        i = e + 1 + 16
+    assert names == sorted(names)
+    table = np.frombuffer(raw, dtype="<u8", count=h, offset=off)
+    out = {n: np.zeros((h, w), np.float32) for n in names}
+    for y in range(h):
+        o = int(table[y])
+        yy, size = struct.unpack_from("<ii", raw, o)
+        assert yy == y0 + y and size == len(names) * w * 4
+        for k, n in enumerate(names):
+            out[n][y] = np.frombuffer(raw, dtype="<f4", count=w, offset=o + 8 + k * w * 4)
+    assert int(table[-1]) + 8 + len(names) * w * 4 == len(raw)
+    return out
+
+
+def test_exr_writer_round_trips(tmp_path):
+    rng = np.random.default_rng(5)
+    rgb = rng.random((7, 5, 3), dtype=np.float32) * 30.0          # linear radiance, row 0 = bottom
+    rgb[0, 0] = (0.0, 17.0, np.float32(1e-30))
+    host.write_exr(tmp_path / "a.exr", rgb)
+    ch = _read_exr(tmp_path / "a.exr")
+    assert sorted(ch) == ["B", "G", "R"]
+    for k, n in enumerate("RGB"):
+        assert ch[n].tobytes() == np.ascontiguousarray(rgb[::-1, :, k]).tobytes()   # EXR rows run top to bottom
