@@ -448,154 +448,6 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
     wf_flush_counters(p, wk, COUNT);
 }
 
-// ---------------------------------------------------------------- trace with a two-ray pool per lane (opt-in: PTB_WF_POOL=1)
-// Every lane owns WFP_K rays whose traversal state lives in shared memory (reciprocal direction, best hit, link, stack);
-// a warp step still votes ONE phase, but a lane takes part with whichever of its rays is in that phase, so a ray that waits
-// for a leaf step (or has finished) no longer idles its lane during node steps.  Same traversal per ray as k_wf_trace
-// (4-ary nodes, near/far rows by direction sign, sorted hits, entry-distance culling at pop, lowest-index ties): the
-// closest hit is the same pair of bits.
-#ifndef WFP_K
-#define WFP_K 2
-#endif
-#ifndef WFP_STACK
-#define WFP_STACK 4               // stack entries per ray in shared memory; deeper ones go to local memory
-#endif
-template <bool COUNT>
-__global__ void __launch_bounds__(PT_BLOCK, 8) k_wf_trace_pool(const RenderParams p, const int *q_in, const int *n_in, int *cursor, const int3 tune) {
-    const SceneDev &sc = p.sc;
-    const int lane = threadIdx.x & 31, tid = threadIdx.x;
-    const int count = *n_in;
-    Work wk = {0, 0, 0, 0, 0, 0, 0};
-    __shared__ float4 sA[WFP_K][PT_BLOCK];              // ix iy iz best.t
-    __shared__ float4 sB[WFP_K][PT_BLOCK];              // ox oy oz bits(best.tri)
-    __shared__ int4 sC[WFP_K][PT_BLOCK];                // link, sp, near-row bits (nx | ny << 1 | nz << 2), path
-    __shared__ int2 sS[WFP_K][WFP_STACK][PT_BLOCK];
-    int2 deep[WFP_K][PT_LBVH_STACK - WFP_STACK];
-    int st0 = WF_FETCH, st1 = WF_FETCH;
-    bool exhausted = count == 0;
-    for (;;) {
-        if (exhausted) { if (st0 == WF_FETCH) st0 = WF_EXIT; if (st1 == WF_FETCH) st1 = WF_EXIT; }
-        const bool n0 = st0 == WF_NODE || st0 == WF_POP, n1 = st1 == WF_NODE || st1 == WF_POP;
-        const bool l0 = st0 == WF_LEAF, l1 = st1 == WF_LEAF, f0 = st0 == WF_FETCH, f1 = st1 == WF_FETCH;
-        const unsigned bF = __ballot_sync(0xffffffffu, f0 | f1);
-        const unsigned bN = __ballot_sync(0xffffffffu, n0 | n1);
-        const unsigned bL = __ballot_sync(0xffffffffu, l0 | l1);
-        const unsigned bI = __ballot_sync(0xffffffffu, !(n0 | n1));          // lanes with NO node work (they wait during node steps)
-        if ((bF | bN | bL) == 0u) break;
-        // a phase runs when enough LANES have a ray for it (tune.x: an empty slot, tune.y: a ray at a leaf), or when lanes
-        // with no node work at all would otherwise idle (a quarter of the warp), or when nothing else is runnable
-        const int cF = __popc(bF), cN = __popc(bN), cL = __popc(bL);
-        if (cF > 0 && (cF >= tune.x || __popc(bF & bI) >= 8 || (bN | bL) == 0u)) {
-            // ------------------------------------------------------------ FETCH: one ray for one empty slot per lane
-            int base = 0;
-            if (lane == (__ffs(bF) - 1)) base = atomicAdd(cursor, cF);
-            base = __shfl_sync(0xffffffffu, base, __ffs(bF) - 1);
-            if (base + cF >= count) exhausted = true;
-            if (f0 | f1) {
-                const int s = f0 ? 0 : 1;
-                const int j = base + __popc(bF & ((1u << lane) - 1u));
-                int st = WF_EXIT;
-                if (j < count) {
-                    const int path = q_in[j];
-                    const float4 r0 = p.wf_ray0[path], r1 = p.wf_ray1[path];
-                    const float ix = safe_rcp(r0.w), iy = safe_rcp(r1.x), iz = safe_rcp(r1.y);
-                    sA[s][tid] = make_float4(ix, iy, iz, r1.z);              // best = the outlier scan's result (wf_big_scan)
-                    sB[s][tid] = make_float4(r0.x * ix, r0.y * iy, r0.z * iz, r1.w);
-                    const int link = sc.bvh_root;
-                    sC[s][tid] = make_int4(link, 0, (ix < 0.0f ? 1 : 0) | (iy < 0.0f ? 2 : 0) | (iz < 0.0f ? 4 : 0), path);
-                    st = link >= 0 ? WF_NODE : WF_LEAF;
-                }
-                if (s == 0) st0 = st; else st1 = st;
-            }
-        } else if (cN > 0 && cL < tune.y && __popc(bL & bI) < 8) {
-            // ------------------------------------------------------------ NODE steps: every step, the lane's ray that has node work
-#pragma unroll 1
-            for (int k = 0; k < tune.z; ++k) {
-                const bool m0 = st0 == WF_NODE || st0 == WF_POP, m1 = st1 == WF_NODE || st1 == WF_POP;
-                if (m0 | m1) {
-                    const int s = (st0 == WF_NODE || (m0 && st1 != WF_NODE)) ? 0 : 1;       // a ray that is AT a node before one that has to pop
-                    int st = s == 0 ? st0 : st1;
-                    const float4 A = sA[s][tid], B = sB[s][tid];
-                    const int4 C = sC[s][tid];
-                    const float ix = A.x, iy = A.y, iz = A.z, best_t = A.w, ox = B.x, oy = B.y, oz = B.z;
-                    const int nx = C.z & 1, ny = (C.z >> 1) & 1, nz = (C.z >> 2) & 1;
-                    int link = C.x, sp = C.y;
-                    int2 *my_stack = &sS[s][0][tid];
-#define WFP_PUSH(v, d) do { const int2 e_ = make_int2((v), __float_as_int(d)); if (sp < WFP_STACK) my_stack[sp * PT_BLOCK] = e_; \
-                            else if (sp < PT_LBVH_STACK) deep[s][sp - WFP_STACK] = e_; ++sp; } while (0)
-                    if (st == WF_POP) {
-#pragma unroll
-                        for (int attempt = 0; attempt < 2; ++attempt) {
-                            if (st == WF_POP) {
-                                if (sp == 0) {
-                                    float4 *o_ = p.wf_ray1 + C.w;
-                                    o_->z = best_t; o_->w = B.w;
-                                    st = WF_FETCH;
-                                } else {
-                                    --sp;
-                                    const int2 e = sp < WFP_STACK ? my_stack[sp * PT_BLOCK] : deep[s][sp - WFP_STACK];
-                                    if (__int_as_float(e.y) <= best_t) { link = e.x; st = e.x >= 0 ? WF_NODE : WF_LEAF; }
-                                }
-                            }
-                        }
-                    }
-                    if (st == WF_NODE) {
-                        const int t_ = 8 * link;
-                        const float4 Xn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + nx), Xf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + (nx ^ 1));
-                        const float4 Yn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + ny), Yf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + (ny ^ 1));
-                        const float4 Zn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + nz), Zf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + (nz ^ 1));
-                        const float4 LK = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 6);
-                        if (COUNT) wk.box += 4;
-                        float d0, d1, d2, d3;
-#define WFP_SLAB(dk, c) do { float lo_ = fmaxf(fmaxf(fmaf(Xn.c, ix, -ox), fmaf(Yn.c, iy, -oy)), fmaf(Zn.c, iz, -oz));                 \
-                             float hi_ = fminf(fminf(fmaf(Xf.c, ix, -ox), fmaf(Yf.c, iy, -oy)), fmaf(Zf.c, iz, -oz));                 \
-                             lo_ = fmaxf(lo_ * 0.999996f, 0.0f); hi_ = fminf(hi_ * 1.000004f, best_t);                                \
-                             dk = lo_ <= hi_ ? lo_ : PT_NO_HIT; } while (0)
-                        WFP_SLAB(d0, x); WFP_SLAB(d1, y); WFP_SLAB(d2, z); WFP_SLAB(d3, w);
-#undef WFP_SLAB
-                        int k0 = __float_as_int(LK.x), k1 = __float_as_int(LK.y), k2 = __float_as_int(LK.z), k3 = __float_as_int(LK.w);
-#define WFP_CE(da, ka, db, kb) do { const bool sw_ = db < da; const float td_ = sw_ ? db : da; const int tk_ = sw_ ? kb : ka; \
-                                    db = sw_ ? da : db; kb = sw_ ? ka : kb; da = td_; ka = tk_; } while (0)
-                        WFP_CE(d0, k0, d1, k1); WFP_CE(d2, k2, d3, k3); WFP_CE(d0, k0, d2, k2); WFP_CE(d1, k1, d3, k3); WFP_CE(d1, k1, d2, k2);
-#undef WFP_CE
-                        if (d3 < PT_NO_HIT) WFP_PUSH(k3, d3);
-                        if (d2 < PT_NO_HIT) WFP_PUSH(k2, d2);
-                        if (d1 < PT_NO_HIT) WFP_PUSH(k1, d1);
-                        link = k0;
-                        st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP;
-                    }
-#undef WFP_PUSH
-                    sC[s][tid] = make_int4(link, sp, C.z, C.w);
-                    if (s == 0) st0 = st; else st1 = st;
-                }
-            }
-        } else {
-            // ------------------------------------------------------------ LEAF step on the lane's ray that waits for one
-            if (l0 | l1) {
-                const int s = l0 ? 0 : 1;
-                const int4 C = sC[s][tid];
-                const float4 r0 = p.wf_ray0[C.w], r1 = p.wf_ray1[C.w];
-                const V3 P = v3(r0.x, r0.y, r0.z), D = v3(r0.w, r1.x, r1.y);
-                Closest best; best.t = sA[s][tid].w; best.tri = __float_as_int(sB[s][tid].w);
-                const int enc = ~C.x;
-                const int first = enc >> 3, cnt = (enc & 7) + 1;
-                for (int k = 0; k < cnt; ++k) {
-                    const int pos = first + k;
-                    float t;
-                    const bool acc_ = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
-                    if (acc_ & (t > 0.0f) & (t <= best.t)) {
-                        const int tid_ = __ldg(sc.sorted_id + pos);
-                        if (t < best.t || tid_ < best.tri) { best.t = t; best.tri = tid_; }
-                    }
-                }
-                sA[s][tid].w = best.t; sB[s][tid].w = __int_as_float(best.tri);
-                if (s == 0) st0 = WF_POP; else st1 = WF_POP;
-            }
-        }
-    }
-    wf_flush_counters(p, wk, COUNT);
-}
-
 // ---------------------------------------------------------------- host side: the iteration loop
 // The frame's paths are dealt to WF_SUBS independent sub-wavefronts (blocks of 256 pixel ids, round-robin), each with its own
 // queues and its own stream.  The persistent trace kernel of one sub-wavefront fills the machine; when its queue runs dry its
@@ -649,15 +501,6 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     }
     const int per_sm = occ > 0 && occ < want_per_sm ? occ : want_per_sm;
     const int trace_blocks = sms * per_sm;
-    static const int want_pool = getenv("PTB_WF_POOL") ? atoi(getenv("PTB_WF_POOL")) : 0;
-    const bool pool = want_pool && wide && p.sc.bvh4_tex != 0;
-    int pool_blocks = trace_blocks;
-    if (pool) {
-        int occ_p = 0;
-        if (p.count_work) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, k_wf_trace_pool<true>, PT_BLOCK, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, k_wf_trace_pool<false>, PT_BLOCK, 0);
-        pool_blocks = sms * (occ_p > 0 ? occ_p : 4);
-    }
     static const int3 tune = make_int3(getenv("PTB_WF_FETCH_MIN") ? atoi(getenv("PTB_WF_FETCH_MIN")) : WF_FETCH_MIN,
                                        getenv("PTB_WF_LEAF_MIN") ? atoi(getenv("PTB_WF_LEAF_MIN")) : 4,
                                        getenv("PTB_WF_NODE_STEPS") ? atoi(getenv("PTB_WF_NODE_STEPS")) : PT_SCHED_NODE_STEPS);
@@ -683,10 +526,7 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
             // next queue length and the fetch cursor start at zero
             cudaMemsetAsync(ctrl + b, 0, sizeof(int), sj[j]);
             cudaMemsetAsync(ctrl + 2, 0, sizeof(int), sj[j]);
-            if (pool) {
-                if (p.count_work) k_wf_trace_pool<true><<<pool_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
-                else k_wf_trace_pool<false><<<pool_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
-            } else if (p.count_work) {
+            if (p.count_work) {
                 if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
                 else k_wf_trace<true, false><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
             } else {
