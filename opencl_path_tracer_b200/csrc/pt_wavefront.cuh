@@ -529,6 +529,31 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     int host_count[WF_SUBS_MAX];
     bool live[WF_SUBS_MAX];
     sj[0] = st;
+    // PTB_L2_PERSIST=1 (experiment): the wide-node array as a persisting L2 window on the trace streams, so that the path
+    // state streaming through the shade kernel (136 B per path per iteration) does not evict the tree
+    static const int l2_persist = getenv("PTB_L2_PERSIST") ? atoi(getenv("PTB_L2_PERSIST")) : 0;
+    if (l2_persist && wide && p.sc.n_nodes4 > 0) {
+        static int max_persist = -1, max_window = 0;
+        if (max_persist < 0) {
+            cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+            cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+            size_t want = (size_t)p.sc.n_nodes4 * 128;
+            if (l2_persist == 1 || want > (size_t)max_persist) want = (size_t)max_persist;
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+            if (getenv("PTB_VERBOSE")) fprintf(stderr, "ptb: L2 persisting max %d B, window max %d B\n", max_persist, max_window);
+        }
+        size_t bytes = (size_t)p.sc.n_nodes4 * 128;
+        if (bytes > (size_t)max_window) bytes = (size_t)max_window;
+        cudaStreamAttrValue av;
+        memset(&av, 0, sizeof av);
+        av.accessPolicyWindow.base_ptr = const_cast<float4 *>(p.sc.bvh4);
+        av.accessPolicyWindow.num_bytes = bytes;
+        av.accessPolicyWindow.hitRatio = bytes <= (size_t)max_persist ? 1.0f : (float)max_persist / (float)bytes;
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = l2_persist == 1 ? cudaAccessPropertyStreaming : cudaAccessPropertyNormal;
+        cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
+        for (int j = 1; j < subs; ++j) cudaStreamSetAttribute(ws.s[j], cudaStreamAttributeAccessPolicyWindow, &av);
+    }
     if (subs > 1) cudaEventRecord(ws.fork, st);
     for (int j = 0; j < subs; ++j) {
         if (j > 0) { sj[j] = ws.s[j]; cudaStreamWaitEvent(sj[j], ws.fork, 0); }
