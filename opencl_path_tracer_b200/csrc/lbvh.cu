@@ -133,13 +133,17 @@ __global__ void k_morton(const float4 *q0, const float4 *q1, const float4 *q2, i
 
 __global__ void k_gather(const float4 *q0, const float4 *q1, const float4 *q2, const float4 *f0, const float4 *f1, const float4 *f2,
                          const int *vals, int n, float4 *sq0, float4 *sq1, float4 *sq2, float4 *sf0, float4 *sf1, float4 *sf2,
-                         float4 *leaf_lo, float4 *leaf_hi) {
+                         float4 *leaf_lo, float4 *leaf_hi, float4 *rq, float4 *rf) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int i = vals[pos];
     float4 a = q0[i], b = q1[i], c = q2[i];
     sq0[pos] = a; sq1[pos] = b; sq2[pos] = c;
-    sf0[pos] = f0[i]; sf1[pos] = f1[i]; sf2[pos] = f2[i];
+    const float4 fa = f0[i], fb = f1[i], fc = f2[i];
+    sf0[pos] = fa; sf1[pos] = fb; sf2[pos] = fc;
+    const float4 idrow = make_float4(__int_as_float(i), 0.0f, 0.0f, 0.0f);
+    rq[4 * (size_t)pos] = a; rq[4 * (size_t)pos + 1] = b; rq[4 * (size_t)pos + 2] = c; rq[4 * (size_t)pos + 3] = idrow;
+    rf[4 * (size_t)pos] = fa; rf[4 * (size_t)pos + 1] = fb; rf[4 * (size_t)pos + 2] = fc; rf[4 * (size_t)pos + 3] = idrow;
     Box bx = tri_box(a, b, c);
     leaf_lo[pos] = make_float4(bx.lo[0], bx.lo[1], bx.lo[2], 0.0f);
     leaf_hi[pos] = make_float4(bx.hi[0], bx.hi[1], bx.hi[2], 0.0f);
@@ -374,6 +378,7 @@ size_t lbvh_carve(Lbvh *b, Scratch &t, char *base, size_t cap, size_t sort_bytes
     b->sq0 = c.take<float4>(cap); b->sq1 = c.take<float4>(cap); b->sq2 = c.take<float4>(cap);
     b->sf0 = c.take<float4>(cap); b->sf1 = c.take<float4>(cap); b->sf2 = c.take<float4>(cap);
     b->sorted_id = c.take<int>(cap);
+    b->rq = c.take<float4>(4 * cap); b->rf = c.take<float4>(4 * cap);
     b->range = c.take<int2>(cap); b->child = c.take<int2>(cap);
     b->leaf_lo = c.take<float4>(cap); b->leaf_hi = c.take<float4>(cap); b->node_lo = c.take<float4>(cap); b->node_hi = c.take<float4>(cap);
     t.bounds = c.take<unsigned>(8); t.keys = c.take<unsigned long long>(cap); t.keys2 = c.take<unsigned long long>(cap);
@@ -461,7 +466,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     b->n_tree = n - n_big;
     const int m = b->n_tree;                                // triangles under the tree: Morton positions [0, m)
     CK(cub::DeviceRadixSort::SortPairs(t.sort_tmp, sort_bytes, keys, keys2, vals, vals2, n, 0, 64, st));
-    k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, vals2, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi);
+    k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, vals2, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi, b->rq, b->rf);
     CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
     b->launches += 1;
     if (m >= 2) {

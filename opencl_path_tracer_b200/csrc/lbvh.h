@@ -17,6 +17,8 @@ struct Lbvh {
     float4 *sq0, *sq1, *sq2;      // triangles in Morton order, parity layout (vertices + normal)
     float4 *sf0, *sf1, *sf2;      // triangles in Morton order, fast layout (normal, anchor, barycentric gradients)
     int *sorted_id;               // Morton position → upload index
+    float4 *rq, *rf;              // the same triangles as 64-byte records (3 float4 of the layout + (bits(upload index), 0, 0, 0)):
+                                  // a leaf step fetches a triangle with two 256-bit loads, index included
     int root;                     // root link
     // kept for re-emitting with a larger inflation (far-away camera)
     void *range, *child;          // int2 per internal node

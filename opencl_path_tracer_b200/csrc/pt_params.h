@@ -36,6 +36,7 @@ struct SceneDev {
     const float4 *bvh4;           // the same tree collapsed to 4-ary nodes, 8 float4 each (lbvh.cu); null: not usable
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order
+    const float4 *srec;           // Morton-ordered 64-byte triangle records of this flavour's layout + upload index (lbvh.h)
     int n_nodes4;                 // wide nodes in bvh4 (128 bytes each)
     int bvh_root;                 // link of the root (may be a leaf link when n_tris == 1)
     // the same outliers as merged scan primitives (prims.cu) for the fast flavour; n_big_prims == 0: scan the triangles

@@ -270,6 +270,9 @@ enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 #ifndef WF_POSTPONE
 #define WF_POSTPONE 0
 #endif
+#ifndef WF_TRI_RECORDS
+#define WF_TRI_RECORDS 1
+#endif
 #ifndef WF_SPLIT_FETCH
 #define WF_SPLIT_FETCH 1
 #endif
@@ -449,11 +452,22 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                 for (int k = 0; k < cnt; ++k) {
                     const int pos = k < cnt_a ? first_a + k : first_b + (k - cnt_a);
                     float t;
+#if WF_TRI_RECORDS
+                    float4 T0, T1, T2, T3;                           // one 64-byte record: two 256-bit loads, upload index included
+                    ldg8(sc.srec + 4 * (size_t)pos, T0, T1);
+                    ldg8(sc.srec + 4 * (size_t)pos + 2, T2, T3);
+                    const bool acc_ = tri_accept<COUNT>(T0, T1, T2, P, D, t, wk);
+                    if (acc_ & (t > 0.0f) & (t <= best.t)) {
+                        const int tid = __float_as_int(T3.x);
+                        if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
+                    }
+#else
                     const bool acc_ = tri_accept<COUNT>(ldg4(sc.sq0 + pos), ldg4(sc.sq1 + pos), ldg4(sc.sq2 + pos), P, D, t, wk);
                     if (acc_ & (t > 0.0f) & (t <= best.t)) {
                         const int tid = __ldg(sc.sorted_id + pos);
                         if (t < best.t || tid < best.tri) { best.t = t; best.tri = tid; }
                     }
+#endif
                 }
                 pend = 0;
             }

@@ -380,6 +380,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         const int wide_levels = (s.lbvh.max_depth + 1) / 2;
         p.sc.bvh4 = (G.wide_bvh && s.lbvh.n_nodes4 > 0 && 3 * wide_levels + 1 <= 64) ? s.lbvh.bvh4 : nullptr;
         p.sc.n_nodes4 = s.lbvh.n_nodes4;
+        p.sc.srec = fastm ? s.lbvh.rf : s.lbvh.rq;
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
         p.sc.big_first = s.lbvh.n_tree; p.sc.big_count = s.lbvh.n_big;
