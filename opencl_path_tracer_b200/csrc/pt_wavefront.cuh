@@ -274,7 +274,7 @@ enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 #define WF_TRI_RECORDS 1
 #endif
 #ifndef WF_SPLIT_FETCH
-#define WF_SPLIT_FETCH 1
+#define WF_SPLIT_FETCH 3
 #endif
 #ifndef WF_MINB
 #define WF_MINB 8                 // resident blocks per SM the register allocation is held to
@@ -373,23 +373,15 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                         // texture pipe kept it 76 % busy (l1tex__data_pipe_tex_wavefronts, profiles/r01_wf_trace_v7.txt:
                         // one wavefront per lane and fetch) while the LSU pipe sat at 27 %.
                         const int t_ = 8 * link;
-#if WF_SPLIT_FETCH >= 3
-                        { float4 A0, A1; ldg8(nd, A0, A1); Xn = nx ? A1 : A0; Xf = nx ? A0 : A1; }
-#else
-                        Xn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + nx); Xf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + (nx ^ 1));
-#endif
-#if WF_SPLIT_FETCH >= 2
-                        { float4 A0, A1; ldg8(nd + 2, A0, A1); Yn = ny ? A1 : A0; Yf = ny ? A0 : A1; }
-#else
-                        Yn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + ny); Yf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + (ny ^ 1));
-#endif
-#if WF_SPLIT_FETCH >= 1
-                        { float4 A0, A1; ldg8(nd + 4, A0, A1); Zn = nz ? A1 : A0; Zf = nz ? A0 : A1; }
-                        LK = ldg4(nd + 6);
-#else
-                        Zn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + nz); Zf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + (nz ^ 1));
-                        LK = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 6);
-#endif
+                        // WF_SPLIT_FETCH bits: 1 = z rows, 2 = y rows, 4 = x rows as one 256-bit LSU load; 8 = links through the LSU
+                        if (WF_SPLIT_FETCH & 4) { float4 A0, A1; ldg8(nd, A0, A1); Xn = nx ? A1 : A0; Xf = nx ? A0 : A1; }
+                        else { Xn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + nx); Xf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + (nx ^ 1)); }
+                        if (WF_SPLIT_FETCH & 2) { float4 A0, A1; ldg8(nd + 2, A0, A1); Yn = ny ? A1 : A0; Yf = ny ? A0 : A1; }
+                        else { Yn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + ny); Yf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 2 + (ny ^ 1)); }
+                        if (WF_SPLIT_FETCH & 1) { float4 A0, A1; ldg8(nd + 4, A0, A1); Zn = nz ? A1 : A0; Zf = nz ? A0 : A1; }
+                        else { Zn = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + nz); Zf = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 4 + (nz ^ 1)); }
+                        if (WF_SPLIT_FETCH & 8) LK = ldg4(nd + 6);
+                        else LK = tex1Dfetch<float4>(sc.bvh4_tex, t_ + 6);
                     } else {
                         Xn = ldg4(nd + nx); Xf = ldg4(nd + (nx ^ 1)); Yn = ldg4(nd + 2 + ny); Yf = ldg4(nd + 2 + (ny ^ 1));
                         Zn = ldg4(nd + 4 + nz); Zf = ldg4(nd + 4 + (nz ^ 1)); LK = ldg4(nd + 6);
