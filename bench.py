@@ -28,12 +28,12 @@ import numpy as np
 EMIT = print          # replaced by _QuietStdout.emit when run as a script
 # measured once under ncu (never inside a timed run): DRAM bytes of one launch of the dominant kernel, per workload
 NCU_DRAM_BYTES_PER_LAUNCH = {"cornell_1080p_1024spp_d4": 32.8e6,      # 8.35 MB read + 24.46 MB written
-                             "spheres100k_1080p_256spp_d4": 85.8e6}   # k_wf_trace, one iteration: 82.2 MB read + 3.6 MB written
+                             "spheres100k_1080p_256spp_d4": 87.1e6}   # k_wf_trace, one iteration: 83.3 MB read + 3.8 MB written
 NCU_DRAM_SOURCE = {
     "cornell_1080p_1024spp_d4": "dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, ncu --set full (profiles/r01_render_v7.txt); "
                                 "per launch, independent of spp: the per-pixel state is touched once",
     "spheres100k_1080p_256spp_d4": "dram__bytes_read.sum + dram__bytes_write.sum of one k_wf_trace launch (one bounce of every path: 2.07 M rays), "
-                                   "ncu --set full (profiles/r01_wf_trace_v7.txt): the 64 B ray records and the queue; the 15 MB tree stays in L2",
+                                   "ncu --set full (profiles/r01_wf_trace_v9.txt): the 64 B ray records and the queue; the 15 MB tree stays in L2",
 }
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
