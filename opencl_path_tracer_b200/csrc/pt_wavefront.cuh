@@ -7,8 +7,13 @@
 //                  traversal; inside, box steps and leaf steps are phase-scheduled by warp votes
 //     k_wf_shade   one thread per queued path, full warps: hit → material → bounce sampling →
 //                  throughput update (prog.cl:321-366), path end → running mean (prog.cl:379) and the
-//                  NEXT sample's camera ray (prog.cl:384-389) in the same thread; surviving paths are
-//                  appended to the next queue with a warp ballot + one atomic per warp
+//                  NEXT sample's camera ray (prog.cl:384-389) in the same thread; the new ray's scan over the
+//                  LBVH's outlier list (its result travels in the ray record as the traversal's initial best
+//                  hit); surviving paths are appended to the next queue with a warp ballot + one atomic per warp
+// The frame's paths are dealt to 1..4 independent sub-wavefronts (own queues, own stream) whose kernels fill each
+// other's tails (launch_wavefront).  k_wf_trace walks the 4-ary collapse of the LBVH: per node 3 texture fetches (x
+// rows by direction sign, links) + 2 256-bit loads (y, z row pairs), per leaf triangle 2 256-bit loads of a 64-byte
+// record — the L1 data pipes (one wavefront per lane and scattered access), not DRAM, are what the traversal loads.
 // A pixel's samples stay strictly sequential (same RNG order as the megakernel and the reference),
 // so the result is bit-identical to the other pipelines in the parity flavour.
 // Iterations needed: at most spp * iterations (every active path consumes one ray per iteration).
