@@ -93,7 +93,7 @@ struct State {
     int fuse_gen = 1;
     int shard_rank = 0, shard_n = 1, shard_group = 1;
     int sum_mode = 0, count_work = 0;
-    int lbvh_leaf = 4;
+    int lbvh_leaf = 3;
     int merge_prims = 1;
     int parity_filter = 1;
     int wf_subs = 2;                   // PTB_WF_SUBS / ptb_set_wf_subs: sub-wavefronts of the wavefront pipeline (pt_wavefront.cuh)
