@@ -74,3 +74,23 @@ def test_pixel_owner_partitions_the_image():
         assert counts.sum() == 1920 * 1080 and counts.min() > 0
         assert counts.max() - counts.min() <= 1920 * 8               # at most one band of imbalance
     assert multigpu.rank_seed_skip(3, 1920, 1080) == 3 * 1920 * 1080
+
+
+def test_progressive_cadence_and_single_rank_sharing():
+    """Host logic of the progressive tile-split render without a device: launches of `refresh_spp` samples (the last one
+    shorter), a drain after each, `on_refresh` with the running sample count; without a process group
+    share_root_colors is a plain allocation of W*H float4."""
+    class FakePtb:
+        def __init__(self): self.finishes, self.allocs = 0, []
+        def finish(self): self.finishes += 1
+        def alloc(self, n): self.allocs.append(n); return 42
+
+    class FakeScene:
+        def __init__(self): self.launches = []
+        def render_spp(self, n): self.launches.append(n)
+
+    ptb, scene, seen = FakePtb(), FakeScene(), []
+    assert multigpu.render_progressive(scene, ptb, 20, 8, on_refresh=seen.append) == 20
+    assert scene.launches == [8, 8, 4] and seen == [8, 16, 20] and ptb.finishes == 3
+    assert multigpu.share_root_colors(ptb, 16, 9) == 42 and ptb.allocs == [16 * 9 * 16]
+    assert multigpu.render_progressive(scene, ptb, 0, 8) == 0 and scene.launches == [8, 8, 4]
