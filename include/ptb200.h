@@ -79,9 +79,15 @@ size_t ptb_mem_size(ptb_mem m);
 int ptb_ingest_mesh(ptb_mem tris, size_t first_tri, const float *vertices, size_t n_verts, const int *indices,
                     const int *mat_ids, size_t n_faces, const float *pos, const float *scale, float pitch_deg,
                     float yaw_deg, int mat_offset);
-/* extensions for hosts that own device memory already (torch tensors, NCCL buffers) */
+/* extensions for hosts that own device memory already (torch tensors, NCCL buffers).  The library cannot see writes
+ * that bypass it: what it derives from a buffer's CONTENTS (the staged SoA copy + LBVH of a triangle buffer, the largest
+ * material index, the "all RNG states are non-negative" scan of rnds) is computed at the first launch after a content
+ * change it knows of — ptb_write, ptb_ingest_mesh, ptb_device_ptr (the caller may write through the pointer) — and
+ * reused until the next one.  A host that rewrites wrapped memory itself (a torch op, a peer GPU, NCCL) calls
+ * ptb_invalidate(mem) afterwards; without it the next launch renders the scene as it was when first staged. */
 ptb_mem ptb_wrap_device(void *device_ptr, size_t bytes);  /* non-owning handle */
 void *ptb_device_ptr(ptb_mem m);
+int ptb_invalidate(ptb_mem m);                             /* "the contents changed behind the library's back" */
 /* Peer memory over NVLink (one process per GPU): the owner exports a ptb_alloc'ed buffer as a 64-byte CUDA IPC handle,
  * a process on another GPU of the box imports it and binds it as a kernel argument like any other buffer.  Used by the
  * tile split: every rank's path kernel stores its pixels' colors[] straight into rank 0's frame, so the
@@ -120,8 +126,10 @@ enum {
 enum {
     PTB_PIPE_MEGAKERNEL = 0,   /* one persistent kernel, path regeneration inside the loop              */
     PTB_PIPE_WAVEFRONT = 1,    /* generate / intersect / shade kernels over compacted ray queues        */
-    PTB_PIPE_AUTO = 2          /* default — the faster one by measurement: megakernel for the
-                                  shared-memory brute force, wavefront for the LBVH                         */
+    PTB_PIPE_AUTO = 2,         /* default — the faster one by measurement               */
+    PTB_PIPE_POOL = 3          /* LBVH scenes: ONE persistent kernel whose warps regroup a pool of ray slots (traversal state in
+                                  shared memory) by phase — node / leaf / shade — every step; no queues, no host loop:
+                                  ptb_render is one launch.  Other scenes: as PTB_PIPE_MEGAKERNEL            */
 };
 int ptb_set_accel(int accel);
 int ptb_set_math(int math);
@@ -136,7 +144,7 @@ int ptb_set_wf_subs(int n);
  * differing launch in between runs the deferred gen_ray as its own kernel first.  0 = run the two
  * kernels literally.  Results are identical either way. */
 int ptb_set_fuse_gen(int on);
-int ptb_set_lbvh_leaf(int max_tris); /* 1..8 triangles per LBVH leaf (default 4); takes effect at the next build */
+int ptb_set_lbvh_leaf(int max_tris); /* 1..8 triangles per LBVH leaf (default 3); takes effect at the next build */
 /* Fast flavour, brute-force scan only: merge coplanar same-material triangle pairs that form a convex quad
  * (a fan-triangulated quad, main.cpp:558) into one scan primitive (default 1).  Never used by PTB_MATH_PARITY. */
 int ptb_set_merge_prims(int on);
@@ -156,14 +164,14 @@ int ptb_build_accel(void);     /* force the (lazy) staging + LBVH build now; ret
  * The image argument (arg 0) is written once at the end when present. */
 int ptb_render(int spp);
 
-/* Restrict the next launches to a pixel subset — the multi-GPU tile split
- * (rank r of n renders interleaved groups of `group` consecutive pixel ids:
- * id/group % n == r).  n==1 restores the full image. */
 /* Closest hit only, for arbitrary rays: `rays` holds n_rays Ray records (32 B, prog.cl:7-9), `out` receives n_rays pairs
  * {float t; int triangle} with the scene currently bound to trace_ray's arguments, the selected structure
  * (ptb_set_accel), flavour and pipeline — first_intersect / kd_intersect semantics (prog.cl:113-184): smallest t > 0, ties
  * to the lowest upload index; (-1, -1) on a miss.  Blocking.  The test surface for "every structure == brute force". */
 int ptb_closest_hit(ptb_mem rays, size_t n_rays, ptb_mem out);
+/* Restrict the next launches to a pixel subset — the multi-GPU tile split
+ * (rank r of n renders interleaved groups of `group` consecutive pixel ids:
+ * id/group % n == r).  n==1 restores the full image. */
 int ptb_set_pixel_shard(int rank, int nranks, int group);
 /* spp-split support: accumulate plain per-pixel sums (not the running mean) so
  * ranks can be added: colors[id] += sample; combine with ptb_resolve_sum. */
@@ -189,8 +197,41 @@ int ptb_reset_counters(void);
  * the reference image is bottom-up, prog.cl:86-88) into host memory. L==0 maps to black
  * (the reference produces NaN there, prog.cl:265-268). */
 int ptb_resolve_rgba8(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host);
+/* The root's epilogue of a render as ONE pass over the frame ("sum -> mean -> tone-map" fused): colors *= 1/divide_by
+ * in place (divide_by = total samples of a sum-mode accumulation; 1 = colors already holds the mean, left untouched), the
+ * tone-mapped float image into `image` (0 = none; bottom-up and with the reference's NaN for L == 0, exactly what trace_ray
+ * writes to its texture, prog.cl:380) and the 8-bit RGBA picture into dst_host (NULL = none; as ptb_resolve_rgba8).  The tone
+ * map keeps prog.cl's operations and order (no FMA contraction, pow as the correctly rounded float of the double function). */
+int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int mode, ptb_mem image, unsigned char *dst_host);
 /* 3x3 median denoise of prog.cl:391-427 as a standalone pass: colors → image (RGBA float). */
 int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height);
+
+/* ---- multi-GPU, one PROCESS per GPU.  The path shards (pixels and samples are independent, the scene is
+ * read-only and uploaded by every rank); the one exchange step — the SUM of the ranks' float accumulation buffers at a
+ * root — runs over NCCL on the library's stream.  No equivalent in the reference (single device, main.cpp:466,476,506).
+ * Rank 0 makes the 128-byte id (ptb_comm_unique_id) and hands it to the other ranks by whatever control plane the host has
+ * (a file, MPI, torch.distributed); every rank then calls ptb_comm_init after ptb_init.  NCCL is loaded at run time.
+ *   spp-split:  ptb_set_accumulate_sum(1); ptb_render(spp_r) on every rank from its own seed set; ptb_comm_reduce(colors, 0);
+ *               root: ptb_resolve_frame(colors, W, H, total_spp, ...)        — sum -> mean -> tone map in one pass
+ *   tile-split: ptb_set_pixel_shard(rank, n, group); ptb_render(spp); ptb_comm_reduce(colors, 0) (disjoint pixel sets: x + 0 == x,
+ *               an exact gather) or the peer-memory gather of ptb_ipc_export / ptb_ipc_import + ptb_comm_barrier. */
+#define PTB_COMM_ID_BYTES 128
+int ptb_comm_unique_id(void *id_out /* PTB_COMM_ID_BYTES */);
+int ptb_comm_init(int rank, int nranks, const void *unique_id /* PTB_COMM_ID_BYTES */);
+int ptb_comm_ranks(void);                      /* 1 before ptb_comm_init */
+int ptb_comm_rank(void);
+int ptb_comm_reduce(ptb_mem colors, int root); /* in place float SUM over all ranks into root's buffer, asynchronous on the stream */
+int ptb_comm_broadcast(ptb_mem buf, int root); /* root's bytes to every rank (scene replication without a host round trip) */
+int ptb_comm_barrier(void);                    /* every rank's stream has drained up to here; returns when all have */
+int ptb_comm_destroy(void);
+
+/* Checkpoint / resume of a progressive render (the reference keeps this state only in device memory and its read-back
+ * is dead code, main.cpp:727-741): the per-pixel RNG states (trace_ray arg 8), the accumulation buffer (arg 12) and the
+ * sample index (arg 10) of the frame the bound camera (arg 11) describes, as a "PTBC" file.  ptb_load_state writes them
+ * back into the buffers bound to trace_ray, sets arg 10 and returns the sample index: the next launch continues the
+ * running mean and every pixel's random stream as if nothing had happened (8 + 8 samples across a dump == 16 samples). */
+int ptb_save_state(const char *path);
+int ptb_load_state(const char *path, int *sample_out);
 
 /* Stream sharing with a host framework (torch): the shim launches on this CUDA stream. */
 int ptb_set_stream(void *cuda_stream);     /* NULL = the shim's own stream */

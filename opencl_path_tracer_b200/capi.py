@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 KERNEL_GEN_RAY, KERNEL_TRACE_RAY, KERNEL_FILT_IM = 0, 1, 2
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_REFBVH, ACCEL_LBVH = 0, 1, 2, 3
 MATH_PARITY, MATH_FAST = 0, 1
-PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO = 0, 1, 2
+PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO, PIPE_POOL = 0, 1, 2, 3
 
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py against the header text)
 SYMBOLS = [
@@ -21,7 +21,8 @@ SYMBOLS = [
     "ptb_set_fuse_gen", "ptb_set_lbvh_leaf", "ptb_set_merge_prims", "ptb_set_parity_filter", "ptb_scan_prims", "ptb_get_accel", "ptb_build_accel", "ptb_render",
     "ptb_set_pixel_shard", "ptb_set_accumulate_sum", "ptb_resolve_sum", "ptb_set_count_work", "ptb_get_counters",
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
-    "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit",
+    "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit", "ptb_invalidate", "ptb_resolve_frame", "ptb_save_state", "ptb_load_state",
+    "ptb_comm_unique_id", "ptb_comm_init", "ptb_comm_ranks", "ptb_comm_rank", "ptb_comm_reduce", "ptb_comm_broadcast", "ptb_comm_barrier", "ptb_comm_destroy",
 ]
 
 
@@ -68,6 +69,10 @@ def load_library(path=None):
         "ptb_set_stream": (i, [vp]), "ptb_get_stream": (vp, []),
         "ptb_accel_stats": (i, [C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(C.c_float)]),
         "ptb_launch_count": (u64, []),
+        "ptb_invalidate": (i, [u64]), "ptb_resolve_frame": (i, [u64, i, i, i, i, u64, vp]),
+        "ptb_save_state": (i, [cp]), "ptb_load_state": (i, [cp, C.POINTER(i)]),
+        "ptb_comm_unique_id": (i, [vp]), "ptb_comm_init": (i, [i, i, vp]), "ptb_comm_ranks": (i, []), "ptb_comm_rank": (i, []),
+        "ptb_comm_reduce": (i, [u64, i]), "ptb_comm_broadcast": (i, [u64, i]), "ptb_comm_barrier": (i, []), "ptb_comm_destroy": (i, []),
     }
     for name, (res, args) in proto.items():
         fn = getattr(lib, name)
@@ -181,6 +186,10 @@ class Ptb:
     def device_ptr(self, h):
         return self.lib.ptb_device_ptr(h)
 
+    def invalidate(self, h):
+        """tell the library that wrapped memory was rewritten outside of it (a torch op, NCCL, a peer GPU)"""
+        self._ck(self.lib.ptb_invalidate(h), "ptb_invalidate")
+
     def ipc_export(self, h):
         """64-byte CUDA IPC handle of a ptb.alloc'ed buffer (bytes), for a process on another GPU of the box."""
         buf = C.create_string_buffer(64)
@@ -253,6 +262,37 @@ class Ptb:
         out = np.empty((h, w, 4), dtype=np.uint8)
         self._ck(self.lib.ptb_resolve_rgba8(colors, w, h, mode, out.ctypes.data), "ptb_resolve_rgba8")
         return out
+
+    def resolve_frame(self, colors, w, h, divide_by=1, mode=0, image=0, want_rgba8=True):
+        """ptb_resolve_frame: sum -> mean (in place) -> tone-mapped float image -> RGBA8 in one pass; returns the RGBA8 array or None"""
+        out = np.empty((h, w, 4), dtype=np.uint8) if want_rgba8 else None
+        self._ck(self.lib.ptb_resolve_frame(colors, w, h, divide_by, mode, image, out.ctypes.data if want_rgba8 else None), "ptb_resolve_frame")
+        return out
+
+    # -- one process per GPU: NCCL behind the boundary
+    def comm_unique_id(self):
+        buf = C.create_string_buffer(128)
+        self._ck(self.lib.ptb_comm_unique_id(buf), "ptb_comm_unique_id")
+        return buf.raw
+
+    def comm_init(self, rank, nranks, unique_id):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._ck(self.lib.ptb_comm_init(rank, nranks, buf), "ptb_comm_init")
+
+    def comm_ranks(self): return self.lib.ptb_comm_ranks()
+    def comm_rank(self): return self.lib.ptb_comm_rank()
+    def comm_reduce(self, h, root=0): self._ck(self.lib.ptb_comm_reduce(h, root), "ptb_comm_reduce")
+    def comm_broadcast(self, h, root=0): self._ck(self.lib.ptb_comm_broadcast(h, root), "ptb_comm_broadcast")
+    def comm_barrier(self): self._ck(self.lib.ptb_comm_barrier(), "ptb_comm_barrier")
+    def comm_destroy(self): self.lib.ptb_comm_destroy()
+
+    def save_state(self, path):
+        self._ck(self.lib.ptb_save_state(os.fsencode(path)), "ptb_save_state")
+
+    def load_state(self, path):
+        s = C.c_int(0)
+        self._ck(self.lib.ptb_load_state(os.fsencode(path), C.byref(s)), "ptb_load_state")
+        return s.value
 
     def filter_median(self, colors, image, w, h):
         self._ck(self.lib.ptb_filter_median(colors, image, w, h), "ptb_filter_median")

@@ -210,8 +210,10 @@ PT_DEV void brute_smem_pairs(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Clo
 // The same scan over merged primitives (prims.cu): a convex planar quad (two coplanar triangles sharing a
 // diagonal) costs one triangle test: inside iff min(u, v, 1 - u - b*v, 1 - v - a*u) >= 0, with (b, a) = (1, 0)
 // for a lone triangle.  7 float4 per pair, the last holds (-b.x, -b.y, -a.x, -a.y).  best.tri = PRIMITIVE index.
-template <int U>
-PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Closest &best) {
+// COUNT: work counters of the SHIPPING scan: one test per primitive actually tested, stage exits of the quad
+// test in the reference's order (t >= 0, then the half-planes v >= 0 and 1 - u - b*v >= 0); n_valid = primitives without the padding one
+template <int U, bool COUNT = false>
+PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Closest &best, Work *wk = nullptr, int n_valid = 0) {
     const RayPair r = ray_pair(P, V);
     const float2 one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
 #pragma unroll U
@@ -230,6 +232,13 @@ PT_DEV void brute_smem_prims(const float4 *s_pairs, int n_pairs, V3 P, V3 V, Clo
         const float2 v = dot2(make_float2(L4.z, L4.w), make_float2(L5.x, L5.y), make_float2(L5.z, L5.w), px, py, pz);
         const float2 q = __ffma2_rn(v, make_float2(L6.x, L6.y), __ffma2_rn(u, neg1, one));     // 1 - u - b*v
         const float2 w = __ffma2_rn(u, make_float2(L6.z, L6.w), __ffma2_rn(v, neg1, one));     // 1 - v - a*u
+        if (COUNT) {
+            const bool sa = !(t.x < 0.0f), sb = !(t.y < 0.0f) && 2 * j + 1 < n_valid;
+            wk->tri += 1 + (2 * j + 1 < n_valid);
+            wk->tri1 += sa + sb;
+            wk->tri2 += (sa & (v.x >= 0.0f)) + (sb & (v.y >= 0.0f));
+            wk->tri3 += (sa & (v.x >= 0.0f) & (q.x >= 0.0f)) + (sb & (v.y >= 0.0f) & (q.y >= 0.0f));
+        }
         closest_update(best, fminf(fminf(u.x, v.x), fminf(q.x, w.x)) >= 0.0f, t.x, 2 * j);
         closest_update(best, fminf(fminf(u.y, v.y), fminf(q.y, w.y)) >= 0.0f, t.y, 2 * j + 1);
     }
@@ -732,7 +741,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
 #if !PT_PARITY
             if (SMEM == 2) brute_smem_pairs<U>(s_tris, (sc.n_tris + 1) >> 1, rayP, rayD, best); else
             if (SMEM == 3) {
-                brute_smem_prims<U>(s_tris, n_prim_pairs, rayP, rayD, best);     // best.tri = primitive index
+                brute_smem_prims<U, COUNT>(s_tris, n_prim_pairs, rayP, rayD, best, &wk, sc.n_prims);     // best.tri = primitive index
             } else
 #endif
 #if PT_PARITY
@@ -797,6 +806,7 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
 
 #include "pt_sched.cuh"
 #include "pt_wavefront.cuh"
+#include "pt_pool.cuh"
 
 // gen_ray as its own launch (prog.cl:384-389): only for hosts that drive the reference's two-kernel sequence
 __global__ void __launch_bounds__(256) k_gen_ray(const RenderParams p, size_t n) {
@@ -872,6 +882,10 @@ void launch_render(const RenderParams &p, cudaStream_t st) {
     if (p.accel == PT_ACCEL_BRUTE) {
         const bool smem = p.sc.n_tris <= PT_SMEM_MAX_TRIS;
         if (smem) {
+#if !PT_PARITY
+            if (c && p.sc.n_prims > 0) launch_one<PT_ACCEL_BRUTE, true, 3, 1, 2>(p, st);     // the counting build of the SHIPPING scan (merged quads)
+            else
+#endif
             if (c) launch_one<PT_ACCEL_BRUTE, true, 1>(p, st);
 #if !PT_PARITY
             else if (p.sc.n_prims > 0) {                              // same scan over merged convex quads (prims.cu)

@@ -106,12 +106,22 @@ void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
 int launch_wavefront(const RenderParams &p, cudaStream_t s);   // returns the number of kernels launched
 int launch_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, bool wavefront, void *scratch, cudaStream_t s);
+// pt_pool.cuh: the persistent state-regrouping kernel for the LBVH (one launch per render)
+size_t pool_scratch_bytes();
+bool pool_usable(const RenderParams &p);
+int launch_pool(const RenderParams &p, void *scratch, cudaStream_t s);
+int launch_pool_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, void *scratch, cudaStream_t s);
 }
 namespace pt_fast {
 void launch_gen_ray(const RenderParams &p, size_t n, cudaStream_t s);
 void launch_render(const RenderParams &p, cudaStream_t s);
 int launch_wavefront(const RenderParams &p, cudaStream_t s);
 int launch_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, bool wavefront, void *scratch, cudaStream_t s);
+// pt_pool.cuh: the persistent state-regrouping kernel for the LBVH (one launch per render)
+size_t pool_scratch_bytes();
+bool pool_usable(const RenderParams &p);
+int launch_pool(const RenderParams &p, void *scratch, cudaStream_t s);
+int launch_pool_closest_hit(const RenderParams &p, const RefRay *rays, size_t n, float2 *out, void *scratch, cudaStream_t s);
 }
 
 #endif  // PT_PARAMS_H_

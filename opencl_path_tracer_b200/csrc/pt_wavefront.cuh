@@ -58,7 +58,7 @@ PT_DEV void wf_store_ray(const RenderParams &p, int i, V3 P, V3 D, const Closest
 PT_DEV int wf_stage_big(const RenderParams &p, float4 *s_big) {
 #if !PT_PARITY
     const SceneDev &sc = p.sc;
-    const int n_big_pairs = (p.count_work || p.accel != PT_ACCEL_LBVH) ? 0 : (sc.n_big_prims + 1) >> 1;
+    const int n_big_pairs = p.accel != PT_ACCEL_LBVH ? 0 : (sc.n_big_prims + 1) >> 1;
     for (int j = threadIdx.x; j < n_big_pairs; j += blockDim.x) {
         const int ia = 2 * j, ib = 2 * j + 1;
         const bool hb = ib < sc.n_big_prims;
@@ -85,7 +85,8 @@ PT_DEV void wf_big_scan(const RenderParams &p, const float4 *s_big, int n_big_pa
     if (p.accel != PT_ACCEL_LBVH) return;
 #if !PT_PARITY
     if (n_big_pairs > 0) {                            // packed scan over the merged outliers, then primitive -> upload index
-        brute_smem_prims<2>(s_big, n_big_pairs, P, D, best);
+        if (p.count_work) brute_smem_prims<2, true>(s_big, n_big_pairs, P, D, best, &wk, p.sc.n_big_prims);
+        else brute_smem_prims<2>(s_big, n_big_pairs, P, D, best);
         if (best.t < PT_NO_HIT) best.tri = __ldg(p.sc.big_rep + best.tri);
         return;
     }

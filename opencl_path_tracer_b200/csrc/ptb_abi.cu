@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "comm.h"
 #include "ingest.h"
 #include "lbvh.h"
 #include "prims.h"
@@ -108,6 +109,9 @@ struct State {
     PendingGen pending;
     void *wf_blob = nullptr;           // wavefront scratch (ray + path state + queues), grown on demand
     size_t wf_pixels = 0;
+    void *pool_blob = nullptr;         // scratch of the persistent pool kernel (pt_pool.cuh): cursor, stack overflow, path state
+    size_t pool_bytes = 0;
+    int auto_pool = 0;                 // PTB_PIPE_AUTO on LBVH scenes: 1 = the pool kernel, 0 = the wavefront (PTB_AUTO_POOL)
 };
 // immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
 // during static destruction, after which ptb_release still gets called
@@ -188,8 +192,9 @@ __global__ void k_any_negative(const int *v, size_t n, int *flag) {
 // pt_rand_nonneg (pt_math.cuh).
 int seeds_nonneg(MemObj *rnds, size_t n, bool *out) {
     *out = false;
-    // memory owned by someone else (ptb_wrap_device: a torch tensor, an NCCL buffer) can change behind our back: rescan per launch
-    if (!rnds->owned || rnds->seeds_version != rnds->version + 1 || rnds->seeds_checked < n) {
+    // one scan per content version: ptb_write / ptb_device_ptr / ptb_invalidate bump it (the owner of wrapped memory calls
+    // ptb_invalidate after writing it behind the library's back); the kernels themselves only ever store states in [0, 2^31)
+    if (rnds->seeds_version != rnds->version + 1 || rnds->seeds_checked < n) {
         if (!G.counters) return PTB_SUCCESS;
         int *flag = reinterpret_cast<int *>(G.counters + PT_CNT_WORDS);      // spare word behind the work counters
         CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), G.stream));
@@ -354,7 +359,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.parity_filter = G.parity_filter;
     p.wf_sort = G.wf_sort;
     p.wf_subs = G.wf_subs;
-    if (p.accel == PT_ACCEL_BRUTE && fastm && !G.count_work) {
+    if (p.accel == PT_ACCEL_BRUTE && fastm) {
         rc = ensure_prims();
         if (rc) return rc;
         p.sc.pq0 = s.p0; p.sc.pq1 = s.p1; p.sc.pq2 = s.p2; p.sc.prim_ab = s.prim_ab; p.sc.prim_shade = s.prim_shade; p.sc.prim_rep = s.prim_rep; p.sc.n_prims = s.n_prims;
@@ -384,7 +389,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
         p.sc.sorted_id = s.lbvh.sorted_id; p.sc.bvh_root = s.lbvh.root;
         p.sc.big_first = s.lbvh.n_tree; p.sc.big_count = s.lbvh.n_big;
-        if (fastm && !G.count_work && s.n_big_prims > 0) {
+        if (fastm && s.n_big_prims > 0) {
             p.sc.bq0 = s.b0; p.sc.bq1 = s.b1; p.sc.bq2 = s.b2; p.sc.big_ab = s.big_ab; p.sc.big_rep = s.big_rep; p.sc.n_big_prims = s.n_big_prims;
         }
     }
@@ -465,6 +470,31 @@ int run_wavefront(RenderParams &p) {
     return PTB_SUCCESS;
 }
 
+// persistent pool kernel (pt_pool.cuh): does this launch go through it?
+bool want_pool(const RenderParams &p) {
+    if (p.from_rays || p.accel != PT_ACCEL_LBVH) return false;
+    if (!(G.pipe == PTB_PIPE_POOL || (G.pipe == PTB_PIPE_AUTO && G.auto_pool))) return false;
+    return G.math == PTB_MATH_PARITY ? pt_parity::pool_usable(p) : pt_fast::pool_usable(p);
+}
+int ensure_pool_blob() {
+    const size_t need = G.math == PTB_MATH_PARITY ? pt_parity::pool_scratch_bytes() : pt_fast::pool_scratch_bytes();
+    if (need > G.pool_bytes) {
+        cudaFree(G.pool_blob);
+        G.pool_blob = nullptr; G.pool_bytes = 0;
+        CUDA_OK(cudaMalloc(&G.pool_blob, need));
+        G.pool_bytes = need;
+    }
+    return PTB_SUCCESS;
+}
+int run_pool(const RenderParams &p) {
+    int rc = ensure_pool_blob();
+    if (rc) return rc;
+    const int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool(p, G.pool_blob, G.stream) : pt_fast::launch_pool(p, G.pool_blob, G.stream);
+    CUDA_OK(cudaGetLastError());
+    G.launches += (unsigned long long)k;
+    return PTB_SUCCESS;
+}
+
 }  // namespace
 
 extern "C" {
@@ -502,6 +532,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
+    if ((env = getenv("PTB_AUTO_POOL"))) G.auto_pool = atoi(env) ? 1 : 0;
     return PTB_SUCCESS;
 }
 
@@ -509,8 +540,11 @@ int ptb_shutdown(void) {
     if (!G.inited) return PTB_SUCCESS;
     cudaSetDevice(G.device);
     cudaStreamSynchronize(G.stream);
-    for (auto &kv : G.mems)
+    comm_destroy();
+    for (auto &kv : G.mems) {
         if (kv.second.owned) cudaFree(kv.second.dptr);
+        else if (kv.second.ipc) cudaIpcCloseMemHandle(kv.second.dptr);
+    }
     G.mems.clear();
     Staged &s = G.staged;
     cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
@@ -522,6 +556,8 @@ int ptb_shutdown(void) {
     G.counters = nullptr;
     cudaFree(G.wf_blob);
     G.wf_blob = nullptr; G.wf_pixels = 0;
+    cudaFree(G.pool_blob);
+    G.pool_blob = nullptr; G.pool_bytes = 0;
     cudaStreamDestroy(G.own_stream);
     G.own_stream = G.stream = nullptr;
     for (auto &k : G.args) for (auto &a : k) a = Arg();
@@ -703,6 +739,13 @@ ptb_mem ptb_ipc_import(const void *handle_in, size_t bytes) {
     G.mems[h] = m;
     return h;
 }
+int ptb_invalidate(ptb_mem h) {
+    MemObj *m = find(h);
+    if (!m) return PTB_ERR_INVALID_MEM;
+    int rc = G.inited ? flush_pending() : PTB_SUCCESS;
+    m->version++;
+    return rc;
+}
 void *ptb_device_ptr(ptb_mem h) {
     MemObj *m = find(h);
     if (!m) return nullptr;
@@ -771,6 +814,7 @@ int ptb_launch(int k, size_t gx, size_t gy) {
         RenderParams p;
         int rc = make_params(p, gx, gy, 1, !fused);
         if (rc) return rc;
+        if (want_pool(p)) return run_pool(p);
         return run_render(p);
     }
     if (k == PTB_KERNEL_FILT_IM) {
@@ -804,7 +848,7 @@ int ptb_set_math(int math) {
     return PTB_SUCCESS;
 }
 int ptb_set_pipeline(int pipe) {
-    if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT && pipe != PTB_PIPE_AUTO) return PTB_ERR_INVALID_VALUE;
+    if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT && pipe != PTB_PIPE_AUTO && pipe != PTB_PIPE_POOL) return PTB_ERR_INVALID_VALUE;
     G.pipe = pipe;
     return PTB_SUCCESS;
 }
@@ -870,6 +914,7 @@ int ptb_render(int spp) {
     RenderParams p;
     rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
     if (rc) return rc;
+    if (want_pool(p)) return run_pool(p);
     if (G.pipe != PTB_PIPE_MEGAKERNEL && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);   // tiny scenes: the megakernel's shared-memory scan
     return run_render(p);
 }
@@ -889,6 +934,18 @@ int ptb_closest_hit(ptb_mem rays_h, size_t n_rays, ptb_mem out_h) {
     RenderParams p;
     rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, 1, false);
     if (rc) return rc;
+    if (want_pool(p)) {
+        rc = ensure_pool_blob();
+        if (rc) return rc;
+        const int kp = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, G.pool_blob, G.stream)
+                                                 : pt_fast::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, G.pool_blob, G.stream);
+        cudaError_t ep = cudaGetLastError();
+        if (ep == cudaSuccess) ep = cudaStreamSynchronize(G.stream);
+        if (ep != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_closest_hit: %s", cudaGetErrorString(ep));
+        G.launches += (unsigned long long)kp;
+        out->version++;
+        return PTB_SUCCESS;
+    }
     const bool wf = G.pipe != PTB_PIPE_MEGAKERNEL && p.accel == PT_ACCEL_LBVH;
     void *scratch = nullptr;
     if (wf) CUDA_OK(cudaMalloc(&scratch, n_rays * 36 + 64));
@@ -920,7 +977,11 @@ int ptb_resolve_sum(ptb_mem colors_sum, int total_spp) {
     if (!m || total_spp <= 0) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_sum: bad buffer or sample count");
     int rc = flush_pending();
     if (rc) return rc;
-    resolve_scale((float4 *)m->dptr, m->bytes / sizeof(float4), 1.0f / (float)total_spp, G.stream);
+    const size_t n = m->bytes / sizeof(float4);
+    if (n > 0x7fffffffu) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_sum: buffer too large");
+    ResolveSrc src{};
+    src.p[0] = (const float4 *)m->dptr; src.n = 1;
+    resolve_frame(src, 1.0f / (float)total_spp, (int)n, 1, 0, (float4 *)m->dptr, nullptr, nullptr, G.stream);
     CUDA_OK(cudaGetLastError());
     G.launches++;
     m->version++;
@@ -951,20 +1012,32 @@ int ptb_reset_counters(void) {
 }
 
 int ptb_resolve_rgba8(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host) {
+    if (!dst_host) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_rgba8: null destination");
+    return ptb_resolve_frame(colors, width, height, 1, mode, 0, dst_host);
+}
+// The root's epilogue in one pass: sum -> mean -> tone map -> float image + 8-bit RGBA.
+int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int mode, ptb_mem image, unsigned char *dst_host) {
     NEED_INIT();
-    MemObj *m = find(colors);
-    size_t n = (size_t)width * (size_t)height;
-    if (!m || !dst_host || width <= 0 || height <= 0 || m->bytes < n * 16) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_rgba8: bad arguments");
+    MemObj *m = find(colors), *im = image ? find(image) : nullptr;
+    const size_t n = (size_t)(width > 0 ? width : 0) * (size_t)(height > 0 ? height : 0);
+    if (!m || n == 0 || n > 0x7fffffffu || m->bytes < n * 16 || divide_by < 1 || (image && (!im || im->bytes < n * 16)) || (mode != 0 && mode != 1))
+        return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_frame: bad arguments");
     int rc = flush_pending();
     if (rc) return rc;
-    unsigned char *d;
-    CUDA_OK(cudaMalloc((void **)&d, n * 4));
-    resolve_rgba8((const float4 *)m->dptr, width, height, mode, d, G.stream);
+    unsigned char *d = nullptr;
+    if (dst_host) CUDA_OK(cudaMalloc((void **)&d, n * 4));
+    ResolveSrc src{};
+    src.p[0] = (const float4 *)m->dptr; src.n = 1;
+    resolve_frame(src, divide_by > 1 ? 1.0f / (float)divide_by : 1.0f, width, height, mode, divide_by > 1 ? (float4 *)m->dptr : nullptr,
+                  im ? (float4 *)im->dptr : nullptr, d, G.stream);
+    cudaError_t e = cudaGetLastError();
     G.launches++;
-    cudaError_t e = cudaMemcpyAsync(dst_host, d, n * 4, cudaMemcpyDeviceToHost, G.stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    if (divide_by > 1) m->version++;
+    if (im) im->version++;
+    if (e == cudaSuccess && dst_host) e = cudaMemcpyAsync(dst_host, d, n * 4, cudaMemcpyDeviceToHost, G.stream);
+    if (e == cudaSuccess && dst_host) e = cudaStreamSynchronize(G.stream);
     cudaFree(d);
-    if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_resolve_rgba8: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_resolve_frame: %s", cudaGetErrorString(e));
     return PTB_SUCCESS;
 }
 int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height) {
@@ -979,6 +1052,112 @@ int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height) {
     CUDA_OK(cudaGetLastError());
     G.launches++;
     im->version++;
+    return PTB_SUCCESS;
+}
+
+// ---------------------------------------------------------------- one process per GPU: NCCL behind the boundary (comm.cu)
+int ptb_comm_unique_id(void *id_out) {
+    if (!id_out) return fail(PTB_ERR_INVALID_VALUE, "ptb_comm_unique_id: null output");
+    char err[256];
+    if (comm_unique_id(id_out, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    return PTB_SUCCESS;
+}
+int ptb_comm_init(int rank, int nranks, const void *unique_id) {
+    NEED_INIT();
+    if (!unique_id || nranks < 1 || rank < 0 || rank >= nranks) return fail(PTB_ERR_INVALID_VALUE, "ptb_comm_init: bad rank %d of %d or null id", rank, nranks);
+    char err[256];
+    CUDA_OK(cudaSetDevice(G.device));
+    if (comm_init(rank, nranks, unique_id, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    return PTB_SUCCESS;
+}
+int ptb_comm_ranks(void) { return comm_ranks(); }
+int ptb_comm_rank(void) { return comm_rank(); }
+int ptb_comm_reduce(ptb_mem colors, int root) {
+    NEED_INIT();
+    MemObj *m = find(colors);
+    if (!m || root < 0 || root >= comm_ranks()) return fail(PTB_ERR_INVALID_VALUE, "ptb_comm_reduce: bad buffer or root");
+    int rc = flush_pending();
+    if (rc) return rc;
+    if (comm_ranks() == 1) return PTB_SUCCESS;
+    char err[256];
+    if (comm_reduce_sum((float *)m->dptr, m->bytes / sizeof(float), root, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    m->version++;
+    return PTB_SUCCESS;
+}
+int ptb_comm_broadcast(ptb_mem buf, int root) {
+    NEED_INIT();
+    MemObj *m = find(buf);
+    if (!m || root < 0 || root >= comm_ranks()) return fail(PTB_ERR_INVALID_VALUE, "ptb_comm_broadcast: bad buffer or root");
+    int rc = flush_pending();
+    if (rc) return rc;
+    if (comm_ranks() == 1) return PTB_SUCCESS;
+    char err[256];
+    if (comm_broadcast(m->dptr, m->bytes, root, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    m->version++;
+    return PTB_SUCCESS;
+}
+int ptb_comm_barrier(void) {
+    NEED_INIT();
+    int rc = flush_pending();
+    if (rc) return rc;
+    char err[256];
+    if (comm_barrier(G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    return PTB_SUCCESS;
+}
+int ptb_comm_destroy(void) { return comm_destroy(); }
+
+// ---------------------------------------------------------------- checkpoint / resume (the progressive state is exactly colors + rnds + sample index)
+namespace {
+struct CkptHeader { char magic[4]; int32_t version, width, height, sample, iterations; uint32_t pad[2]; };
+}
+int ptb_save_state(const char *path) {
+    NEED_INIT();
+    if (!path) return fail(PTB_ERR_INVALID_VALUE, "ptb_save_state: null path");
+    const int K = PTB_KERNEL_TRACE_RAY;
+    bool ok = true;
+    RefCamera cam = arg_val<RefCamera>(K, 11, &ok);
+    const int sample = arg_val<int>(K, 10, &ok), iterations = arg_val<int>(K, 9, &ok);
+    MemObj *rnds = arg_mem(K, 8), *colors = arg_mem(K, 12);
+    if (!ok || !rnds || !colors) return fail(PTB_ERR_INVALID_ARGS, "ptb_save_state: bind trace_ray's arguments 8-12 first");
+    const size_t n = (size_t)(int)cam.XM * (size_t)(int)cam.YM;
+    if (n == 0 || rnds->bytes < n * 4 || colors->bytes < n * 16) return fail(PTB_ERR_INVALID_ARGS, "ptb_save_state: rnds/colors smaller than the camera's frame");
+    std::vector<unsigned char> host(n * 20);
+    int rc = ptb_read(G.args[K][8].mem, 0, n * 4, host.data());
+    if (rc) return rc;
+    rc = ptb_read(G.args[K][12].mem, 0, n * 16, host.data() + n * 4);
+    if (rc) return rc;
+    CkptHeader h{{'P', 'T', 'B', 'C'}, 1, (int)cam.XM, (int)cam.YM, sample, iterations, {0, 0}};
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(PTB_ERR_INVALID_VALUE, "ptb_save_state: cannot write %s", path);
+    const bool wrote = fwrite(&h, sizeof h, 1, f) == 1 && fwrite(host.data(), 1, host.size(), f) == host.size();
+    if (fclose(f) != 0 || !wrote) return fail(PTB_ERR_INVALID_VALUE, "ptb_save_state: short write to %s", path);
+    return PTB_SUCCESS;
+}
+int ptb_load_state(const char *path, int *sample_out) {
+    NEED_INIT();
+    if (!path) return fail(PTB_ERR_INVALID_VALUE, "ptb_load_state: null path");
+    const int K = PTB_KERNEL_TRACE_RAY;
+    bool ok = true;
+    RefCamera cam = arg_val<RefCamera>(K, 11, &ok);
+    MemObj *rnds = arg_mem(K, 8), *colors = arg_mem(K, 12);
+    if (!ok || !rnds || !colors) return fail(PTB_ERR_INVALID_ARGS, "ptb_load_state: bind trace_ray's arguments 8, 11, 12 first");
+    FILE *f = fopen(path, "rb");
+    if (!f) return fail(PTB_ERR_INVALID_VALUE, "ptb_load_state: cannot read %s", path);
+    CkptHeader h;
+    if (fread(&h, sizeof h, 1, f) != 1 || memcmp(h.magic, "PTBC", 4) || h.version != 1) { fclose(f); return fail(PTB_ERR_INVALID_VALUE, "ptb_load_state: %s is not a PTBC v1 file", path); }
+    if (h.width != (int)cam.XM || h.height != (int)cam.YM) { fclose(f); return fail(PTB_ERR_INVALID_VALUE, "ptb_load_state: checkpoint is %dx%d, the bound camera %dx%d", h.width, h.height, (int)cam.XM, (int)cam.YM); }
+    const size_t n = (size_t)h.width * (size_t)h.height;
+    if (rnds->bytes < n * 4 || colors->bytes < n * 16) { fclose(f); return fail(PTB_ERR_INVALID_ARGS, "ptb_load_state: rnds/colors smaller than the checkpoint's frame"); }
+    std::vector<unsigned char> host(n * 20);
+    const bool got = fread(host.data(), 1, host.size(), f) == host.size();
+    fclose(f);
+    if (!got) return fail(PTB_ERR_INVALID_VALUE, "ptb_load_state: %s is truncated", path);
+    int rc = ptb_write(G.args[K][8].mem, 0, n * 4, host.data());
+    if (rc) return rc;
+    rc = ptb_write(G.args[K][12].mem, 0, n * 16, host.data() + n * 4);
+    if (rc) return rc;
+    ptb_set_arg(K, 10, sizeof(int), &h.sample);          // the next launch continues at the checkpoint's sample index
+    if (sample_out) *sample_out = h.sample;
     return PTB_SUCCESS;
 }
 

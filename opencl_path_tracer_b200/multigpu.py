@@ -61,6 +61,40 @@ def merge_tile_split(local_colors, group=None):
     return local_colors
 
 
+def comm_init_from_dist(ptb, group=None):
+    """Bring up the LIBRARY's communicator (ptb_comm_init: NCCL on the library's own stream) for the ranks of a
+    torch.distributed process group: rank 0 makes the 128-byte id, the group carries it to the others (control plane
+    only).  After this the data-path exchange is ptb.comm_reduce / ptb.comm_barrier — no torch collective touches a pixel."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return False
+    rank = dist.get_rank(group)
+    payload = [ptb.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(payload, src=0, group=group)
+    ptb.comm_init(rank, dist.get_world_size(group), payload[0])
+    return True
+
+
+def split_spp(total_spp, nranks, rank):
+    """samples of a FIXED total job that rank renders under the spp-split (strong scaling): the first total % n ranks take one more"""
+    return total_spp // nranks + (1 if rank < total_spp % nranks else 0)
+
+
+def release_shared_colors(ptb, handle, group=None):
+    """Counterpart of share_root_colors: nobody may still be storing into the root's buffer when it is freed, and the peers'
+    mappings must be closed before the allocation goes away (CUDA IPC rules)."""
+    ptb.finish()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.barrier(group=group)
+        rank = dist.get_rank(group)
+        if rank != 0:
+            ptb.release(handle)
+        dist.barrier(group=group)
+        if rank == 0:
+            ptb.release(handle)
+    else:
+        ptb.release(handle)
+
+
 def share_root_colors(ptb, width, height, group=None, root=0):
     """Peer-memory gather of the tile split: returns a ptb handle to bind as ``colors`` (``scene.buffer_colors``).  On
     ``root`` it is a fresh ptb.alloc'ed W*H float4 buffer; on every other rank it is that same memory mapped through
@@ -74,6 +108,7 @@ def share_root_colors(ptb, width, height, group=None, root=0):
     h = None
     if rank == root:
         h = ptb.alloc(nbytes)
+        ptb.finish()                      # the allocation's zero-fill has completed before any peer can store into it
         payload = [ptb.ipc_export(h)]
     dist.broadcast_object_list(payload, src=root, group=group)
     if rank != root:
@@ -103,6 +138,10 @@ def render_progressive(scene, ptb, total_spp, refresh_spp, on_refresh=None, grou
         done += n
         if on_refresh is not None:
             on_refresh(done)
+            # the root reads the shared frame inside on_refresh: nobody launches the next samples (which store into that
+            # same buffer over NVLink) before it is done — otherwise a refresh could mix pixels at `done` and `done + n` samples
+            if dist.is_initialized() and dist.get_world_size(group) > 1:
+                dist.barrier(group=group)
     return done
 
 

@@ -300,6 +300,44 @@ void pto_render(const pto_scene *s, int32_t first_sample, int32_t spp, int32_t t
         }
 }
 
+/* ---------------------------------------------------------------- prog.cl:259-263 */
+void pto_filmic(const float *rgb3, float *rgba4) {
+    for (int k = 0; k < 3; ++k) {
+        float c = fmaxf(0.0f, rgb3[k] - 0.004f);
+        rgba4[k] = (c * (c * 6.2f + 0.5f)) / (c * (c * 6.2f + 1.7f) + 0.06f);
+    }
+    rgba4[3] = 1.0f;
+}
+
+/* ---------------------------------------------------------------- prog.cl:391-427 (launch: main.cpp:665-668, commented there)
+ * One work-item per pixel over (width, height): 3x3 neighbourhood through LINEAR ids (y-1+i)*width + (x-1+j), selection
+ * sort by grey value (strict '>' : the first maximum wins), element 4 of the sorted order, filmic tone map.  The guard is
+ * the reference's x>0 && y>0 (x<width, y<height hold for every work-item); work-items whose neighbourhood would run past
+ * the end of colors[] (the last scanline, and the last pixel of the one before) read out of range in the reference and
+ * are skipped here.  tex: W*H*4 floats, untouched where nothing is written. */
+void pto_filt_im(const pto_f3 *colors, float *tex, int32_t width, int32_t height) {
+    const int64_t n = (int64_t)width * height;
+    for (int y = 0; y < height; ++y)
+        for (int x = 0; x < width; ++x) {
+            if (!(x > 0 && y > 0)) continue;
+            if ((int64_t)(y + 1) * width + (x + 1) >= n) continue;
+            pto_f3 arr[9];
+            float grey[9];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) arr[i * 3 + j] = colors[(int64_t)(y - 1 + i) * width + (x - 1 + j)];
+            for (int i = 0; i < 9; ++i) grey[i] = (arr[i].x + arr[i].y + arr[i].z) / 3.0f;
+            for (int j = 9; j > 1; j--) {
+                int maxi = 0;
+                for (int i = 1; i < j; ++i)
+                    if (grey[i] > grey[maxi]) maxi = i;
+                float tg = grey[j - 1]; grey[j - 1] = grey[maxi]; grey[maxi] = tg;
+                pto_f3 ta = arr[j - 1]; arr[j - 1] = arr[maxi]; arr[maxi] = ta;
+            }
+            const float med[3] = {arr[4].x, arr[4].y, arr[4].z};
+            pto_filmic(med, tex + 4 * ((int64_t)y * width + x));
+        }
+}
+
 int pto_struct_sizes(int32_t *o) {
     o[0] = sizeof(pto_material); o[1] = sizeof(pto_ray); o[2] = sizeof(pto_triangle);
     o[3] = sizeof(pto_node); o[4] = sizeof(pto_camera); o[5] = sizeof(pto_f3);

@@ -51,5 +51,7 @@ void pto_render(const pto_scene *s, int32_t first_sample, int32_t spp, int32_t t
 float pto_closest_hit(const pto_scene *s, const float *origin3, const float *dir3, int32_t *tri_index);
 void pto_minstd_rand0(int32_t *out, int64_t count, int64_t skip);         /* main.cpp:45,522-526 */
 float pto_reinhard(const float *rgb3, float *rgba4);                      /* prog.cl:247-258,264-269 */
+void pto_filmic(const float *rgb3, float *rgba4);                         /* prog.cl:259-263 */
+void pto_filt_im(const pto_f3 *colors, float *tex, int32_t width, int32_t height);   /* prog.cl:391-427 over (width, height) */
 int pto_struct_sizes(int32_t *out6);                                      /* Material Ray Triangle Node Camera f3 */
 #endif

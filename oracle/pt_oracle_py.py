@@ -69,6 +69,17 @@ def struct_sizes():
     return dict(zip(["Material", "Ray", "Triangle", "Node", "Camera", "float3"], o.tolist()))
 
 
+def filt_im(colors, width, height):
+    """prog.cl:391-427 over a (H, W, 4) float32 accumulation buffer: returns the (H, W, 4) RGBA float image, zero where the
+    kernel writes nothing."""
+    c = np.ascontiguousarray(colors, dtype=np.float32).reshape(height * width * 4)
+    tex = np.zeros(height * width * 4, dtype=np.float32)
+    fn = lib().pto_filt_im
+    fn.restype, fn.argtypes = None, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
+    fn(c.ctypes.data, tex.ctypes.data, width, height)
+    return tex.reshape(height, width, 4)
+
+
 class OracleScene:
     """The kernel-argument surface (a dict as returned by host.load_ptbd / built by the host mirror) bound to the C oracle."""
 

@@ -211,6 +211,29 @@ void launch_trace_ray(size_t W, size_t H) {
         launch_trace_ray_ns<refcl::Triangle, refcl::Material, refcl::Node, refcl::Ray, refcl::Camera>(W, H, refcl::trace_ray);
 }
 
+// filt_im(tex, colors) — prog.cl:391-427, enqueued 2-D (W,H) in the reference's commented launch (main.cpp:665-668).
+// The kernel guards x>0 && y>0 && x<width && y<height and then reads the 3x3 neighbourhood through LINEAR ids
+// (y-1+i)*width + (x-1+j): on the last column that wraps into the next scanline (defined in a linear buffer), on the last
+// scanline — and for the very last pixel of the scanline before it — it reads past the end of colors[] (undefined in the
+// reference).  The executor runs every work-item whose nine reads stay inside the buffer and skips the others.
+void launch_filt_im(size_t W, size_t H) {
+    const int K = PTB_KERNEL_FILT_IM;
+    Mem *img = find(g_args[K][0].mem);
+    oclshim::image2d_t tex = (img && img->is_image) ? &img->img : nullptr;
+    Mem *cm = find(g_args[K][1].mem);
+    if (!tex || !cm || cm->bytes.size() < W * H * sizeof(oclshim::float3)) { fail(PTB_ERR_INVALID_ARGS, "filt_im: image / colors argument missing"); return; }
+    auto *colors = reinterpret_cast<oclshim::float3 *>(cm->bytes.data());
+    parallel_rows(H, [&](size_t y) {
+        oclshim::WorkItem &wi = oclshim::work_item();
+        wi.gsz[0] = W; wi.gsz[1] = H; wi.gsz[2] = 1; wi.gid[1] = y; wi.gid[2] = 0;
+        for (size_t x = 0; x < W; ++x) {
+            if ((y + 1) * W + (x + 1) >= W * H) continue;      // would read colors[] out of range
+            wi.gid[0] = x;
+            refcl::filt_im(tex, colors);
+        }
+    });
+}
+
 }  // namespace
 
 // unit-level entry points used by the oracle self-checks (tests/, not-gpu): the reference's own rand()
@@ -318,6 +341,7 @@ int ptb_launch(int k, size_t gx, size_t gy) {
     g_launches++;
     if (k == PTB_KERNEL_GEN_RAY) launch_gen_ray(gx * (gy ? gy : 1));
     else if (k == PTB_KERNEL_TRACE_RAY) launch_trace_ray(gx, gy);
+    else if (k == PTB_KERNEL_FILT_IM) launch_filt_im(gx, gy);
     else return fail(PTB_ERR_INVALID_KERNEL, "ptb_launch: kernel not available in the CPU oracle");
     return g_err.empty() ? PTB_SUCCESS : PTB_ERR_INVALID_ARGS;
 }
@@ -356,7 +380,11 @@ int ptb_reset_counters(void) {
     return PTB_SUCCESS;
 }
 int ptb_resolve_rgba8(ptb_mem, int, int, int, unsigned char *) { return PTB_ERR_INVALID_VALUE; }
-int ptb_filter_median(ptb_mem, ptb_mem, int, int) { return PTB_ERR_INVALID_VALUE; }
+int ptb_filter_median(ptb_mem colors, ptb_mem image, int w, int h) {
+    ptb_set_arg_mem(PTB_KERNEL_FILT_IM, 0, image);
+    ptb_set_arg_mem(PTB_KERNEL_FILT_IM, 1, colors);
+    return ptb_launch(PTB_KERNEL_FILT_IM, (size_t)w, (size_t)h);
+}
 int ptb_set_stream(void *) { return PTB_SUCCESS; }
 void *ptb_get_stream(void) { return nullptr; }
 int ptb_accel_stats(int *a, int *b, int *c, float *d) {

@@ -105,7 +105,7 @@ int main(int argc, char **argv) {
     float fov = 39.3f, cyaw = 0.0f, cpitch = 0.0f, eye[3] = {277.5f, 277.5f, -800.0f};
     std::vector<ObjSpec> objs;
     std::vector<std::string> tribins;
-    std::string out, dump, rnds_out, tex_out;
+    std::string out, dump, rnds_out, tex_out, filt_out, colors_in;
     auto need = [&](int &i, int n) { if (i + n >= argc) { fprintf(stderr, "missing value after %s\n", argv[i]); exit(2); } };
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -135,6 +135,8 @@ int main(int argc, char **argv) {
         else if (a == "--dump") { need(i, 1); dump = argv[++i]; }
         else if (a == "--rnds-out") { need(i, 1); rnds_out = argv[++i]; }
         else if (a == "--tex-out") { need(i, 1); tex_out = argv[++i]; }
+        else if (a == "--filt-out") { need(i, 1); filt_out = argv[++i]; }
+        else if (a == "--colors-in") { need(i, 1); colors_in = argv[++i]; }
         else { fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
     // screen_width/height are `const int` globals initialised before main (main.cpp:20-21, patched to
@@ -209,6 +211,28 @@ int main(int argc, char **argv) {
         std::vector<cl_float4> t(n);
         scene.queue.enqueueReadBuffer(scene.cl_screen, CL_TRUE, 0, n * sizeof(cl_float4), t.data());
         write_file(tex_out, t.data(), n * sizeof(cl_float4));
+    }
+    if (!filt_out.empty()) {
+        // the launch the reference keeps commented out at main.cpp:665-668, verbatim: filt_im(cl_screen, buffer_colors) over (W, H);
+        // --colors-in replaces the rendered accumulation buffer by a raw float4 file first (arbitrary test images)
+        if (!colors_in.empty()) {
+            std::vector<cl_float3> c(n);
+            FILE *f = fopen(colors_in.c_str(), "rb");
+            if (!f || fread(c.data(), sizeof(cl_float3), n, f) != n) { fprintf(stderr, "cannot read %zu pixels from %s\n", n, colors_in.c_str()); return 2; }
+            fclose(f);
+            scene.queue.enqueueWriteBuffer(scene.buffer_colors, CL_TRUE, 0, n * sizeof(cl_float3), c.data());
+        }
+        std::vector<cl_float4> zero(n);
+        memset(zero.data(), 0, n * sizeof(cl_float4));
+        ptb_write(scene.cl_screen(), 0, n * sizeof(cl_float4), zero.data());      // pixels filt_im leaves alone read back as 0
+        cl::Kernel kernel_filt_im = cl::Kernel(scene.program, "filt_im");
+        kernel_filt_im.setArg(0, scene.cl_screen);
+        kernel_filt_im.setArg(1, scene.buffer_colors);
+        scene.queue.enqueueNDRangeKernel(kernel_filt_im, cl::NullRange, cl::NDRange(screen_width, screen_height), cl::NullRange);
+        scene.queue.finish();
+        std::vector<cl_float4> t(n);
+        scene.queue.enqueueReadBuffer(scene.cl_screen, CL_TRUE, 0, n * sizeof(cl_float4), t.data());
+        write_file(filt_out, t.data(), n * sizeof(cl_float4));
     }
     if (!dump.empty()) {
         // "PTBD": the kernel-argument surface exactly as the reference host uploaded it

@@ -43,6 +43,32 @@ def main():
     subprocess.run([REF, "--w", "80", "--h", "60", "--spp", "0", "--iterations", "6", "--dump", os.path.join(HERE, "small_mixed_80x60.ptbd")] + mixed, check=True, capture_output=True)
     run("small_mixed_80x60_spp4_d6", 80, 60, 4, 6, mixed)
     os.remove(ptbs)
+    filt_im_fixture(cornell)
+
+
+def tie_image(w, h, seed=11):
+    """random radiance with what makes the reference's unstable selection sort matter (prog.cl:410-424): runs of pixels with
+    EQUAL grey value and different colours, flat black areas, repeated pixels"""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    img = np.zeros((h, w, 4), dtype=np.float32)
+    img[..., :3] = rng.random((h, w, 3), dtype=np.float32) * 2.0
+    ties = np.array([(1, 2, 3), (3, 2, 1), (2, 2, 2), (0, 3, 3), (6, 0, 0), (2, 1, 3)], dtype=np.float32)
+    img[4:14, 5:25, :3] = ties[rng.integers(0, len(ties), size=(10, 20))]
+    img[16:24, 10:30, :3] = 0.0
+    img[20:30, 28:44, :3] = ties[rng.integers(0, 3, size=(10, 16))]
+    img[26:, :8, :3] = img[26, 0, :3]
+    return img
+
+
+def filt_im_fixture(cornell):
+    """filt_im_48x32.{in,out}.f32: the reference's own filt_im kernel (prog.cl:391-427, launched as main.cpp:665-668 would)
+    on an image with constructed ties; pixels the kernel does not write stay 0"""
+    base = os.path.join(HERE, "filt_im_48x32")
+    tie_image(48, 32).tofile(base + ".in.f32")
+    subprocess.run([REF, "--w", "48", "--h", "32", "--spp", "0", "--colors-in", base + ".in.f32", "--filt-out", base + ".out.f32"] + cornell,
+                   check=True, capture_output=True)
+    print("filt_im_48x32 written")
 
 
 if __name__ == "__main__":

@@ -28,7 +28,8 @@ def test_reference_arm_prints_one_json_line():
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
-    assert d["config"]["workload"] == "cornell_512_16spp_d4" and "sample" in d["config"]
+    assert d["config"]["workload"] == "cornell_512_16spp_d4" and d["config"]["triangles"] == 32 and d["config"]["spp"] == 16
+    assert "sample" in d["cpu_baseline"] and "fair" in d["cpu_baseline"]
 
 
 def test_reference_arm_on_a_generated_scene_uses_the_port():

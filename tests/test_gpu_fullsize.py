@@ -77,7 +77,7 @@ def test_c2_samples_split_over_launches_is_bitwise_the_same(ptb, c2_parity_64):
 
 
 @pytest.mark.parametrize("accel,pipeline", [(capi.ACCEL_LBVH, capi.PIPE_MEGAKERNEL), (capi.ACCEL_LBVH, capi.PIPE_WAVEFRONT),
-                                            (capi.ACCEL_REFBVH, capi.PIPE_MEGAKERNEL)])
+                                            (capi.ACCEL_LBVH, capi.PIPE_POOL), (capi.ACCEL_REFBVH, capi.PIPE_MEGAKERNEL)])
 def test_c2_closest_hit_structure_and_pipeline_do_not_change_a_bit(ptb, c2_parity_64, accel, pipeline):
     s = cornell(ptb, accel, capi.MATH_PARITY, pipeline)
     s.render_spp(64)
@@ -159,7 +159,7 @@ def test_c3_lbvh_pipelines_agree_bitwise_at_1080p(ptb):
     megakernel loop is the tested one at small size against the oracle, tests/test_gpu_parity.py) must agree bitwise"""
     d = scenes.describe("spheres100k")
     out = []
-    for pipeline in (capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT):
+    for pipeline in (capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL):
         ptb.set_accel(capi.ACCEL_LBVH); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(pipeline)
         s = host.Scene(ptb)
         s.build_trees = False
@@ -172,7 +172,8 @@ def test_c3_lbvh_pipelines_agree_bitwise_at_1080p(ptb):
         s.render_spp(4)
         out.append((s.download_colors().copy(), s.download_rnds().copy()))
         release(s)
-    assert (bits(out[0][0]) == bits(out[1][0])).all() and (out[0][1] == out[1][1]).all()
+    for o in out[1:]:
+        assert (bits(out[0][0]) == bits(o[0])).all() and (out[0][1] == o[1]).all()
     assert out[0][0][..., :3].mean() > 0
 
 

@@ -145,8 +145,9 @@ def test_mixed_materials_parity(ptb, mixed_ref, accel):
 def test_mixed_materials_fast(ptb, mixed_ref):
     colors, _ = render(ptb, mixed_ref, capi.ACCEL_LBVH, capi.MATH_FAST, "render_spp", spp=8)
     st = util.compare(colors, mixed_ref["colors"])
-    assert st["frac_rel_le_1e-4"] >= 0.995, st          # glass/mirror chains amplify rounding: 99.5 % here
-    assert st["rmse_over_mean"] <= 0.05, st
+    print("mixed fast vs reference:", st)
+    assert st["frac_rel_le_1e-4"] >= 0.999, st
+    assert st["rmse_over_mean"] <= 0.01, st
 
 
 # ---------------------------------------------------------------- 100 k triangles: LBVH == reference trees == oracle
@@ -191,13 +192,34 @@ def test_reference_host_over_cuda_shim(tmp_path):
 
 
 # ---------------------------------------------------------------- wavefront pipeline == megakernel == oracle
+@pytest.mark.parametrize("pipeline", [capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
 @pytest.mark.parametrize("which", ["mixed", "spheres"])
-def test_wavefront_parity(ptb, mixed_ref, spheres_ref, which):
+def test_wavefront_parity(ptb, mixed_ref, spheres_ref, which, pipeline):
     ref, spp = (mixed_ref, 8) if which == "mixed" else (spheres_ref, 4)
-    colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp, pipeline=capi.PIPE_WAVEFRONT)
+    colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp, pipeline=pipeline)
     st = util.compare(colors, ref["colors"])
     assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
     assert (rnds == ref["rnds"]).mean() >= 1.0 - 1e-4
+
+
+@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
+def test_spheres100k_fast_flavour_against_the_reference(ptb, spheres_ref, pipeline):
+    """the SHIPPING configuration of the LBVH scenes (fast arithmetic, merged outlier quads scanned from shared memory, `rf`
+    triangle records, rcp.approx t) against the reference's own kernels on the 104 k-triangle scene, stated tolerance"""
+    colors, rnds = render(ptb, spheres_ref, capi.ACCEL_LBVH, capi.MATH_FAST, "render_spp", spp=4, pipeline=pipeline)
+    st = util.compare(colors, spheres_ref["colors"])
+    assert st["frac_rel_le_1e-4"] >= 0.999 and st["rmse_over_mean"] <= 0.01, st
+    assert (rnds == spheres_ref["rnds"]).mean() >= 0.999
+
+
+@pytest.mark.parametrize("mode", ["fused_launches", "render_spp"])
+def test_pool_kernel_on_cornell_is_bit_identical(ptb, cornell_ref, mode):
+    """the persistent pool kernel (PTB_PIPE_POOL) forced onto the 32-triangle scene through the LBVH: per-sample launches
+    (gen_ray folded in, one kernel launch per sample) and the in-kernel sample loop"""
+    colors, rnds = render(ptb, cornell_ref, capi.ACCEL_LBVH, capi.MATH_PARITY, mode, pipeline=capi.PIPE_POOL)
+    st = util.compare(colors, cornell_ref["colors"])
+    assert st["bit_equal_frac"] == 1.0, st
+    assert (rnds == cornell_ref["rnds"]).all()
 
 
 # ---------------------------------------------------------------- scene ingest on the device (SURVEY §8f row 3)

@@ -79,7 +79,7 @@ def test_every_structure_equals_brute_force_on_random_rays(ptb, math, scene, dup
     assert (want[1] >= 0).mean() > 0.5            # closed rooms: most rays hit something
     try:
         ptb.set_merge_prims(0)                    # (fast flavour: plain triangles first — same test code as brute force, so exact)
-        for accel, pipe in ((capi.ACCEL_LBVH, capi.PIPE_MEGAKERNEL), (capi.ACCEL_LBVH, capi.PIPE_WAVEFRONT)):
+        for accel, pipe in ((capi.ACCEL_LBVH, capi.PIPE_MEGAKERNEL), (capi.ACCEL_LBVH, capi.PIPE_WAVEFRONT), (capi.ACCEL_LBVH, capi.PIPE_POOL)):
             ptb.set_accel(accel); ptb.set_pipeline(pipe)
             assert same(ptb.closest_hit(o, dirs), want), (accel, pipe)
     finally:
@@ -127,6 +127,8 @@ def test_sample_of_the_rays_against_the_c_oracle(ptb):
     rng = np.random.default_rng(11)
     o, dirs = random_rays(rng, 4000, v.min(axis=0), v.max(axis=0), s.tris)
     got = ptb.closest_hit(o, dirs)
+    ptb.set_pipeline(capi.PIPE_POOL)
+    assert same(ptb.closest_hit(o, dirs), got)
     surf = {"W": 64, "H": 64, "iterations": 1, "camera": host.camera_at(64, 64, 60.0, 0, 0, (0.0, 0.0, -10.0)), "tris": s.tris,
             "mats": np.stack(s.mats), "kd_tree": host.nodes_to_records(s.kd_tree), "kd_tree_shift": np.asarray(s.kd_tree_shift, dtype=np.int32)}
     orc = po.OracleScene(surf, brute=True)

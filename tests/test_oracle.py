@@ -95,3 +95,25 @@ def test_samples_are_sequential_per_pixel():
     b = po.OracleScene(surf)
     b.render(5, 1)
     assert a.colors.tobytes() == b.colors.tobytes() and (a.rnds == b.rnds).all()
+
+
+def test_filt_im_port_reproduces_the_reference_kernel_fixture():
+    # tests/golden/filt_im_48x32.*: the reference's own filt_im (prog.cl:391-427) on an image with constructed grey ties
+    src = np.fromfile(os.path.join(G, "filt_im_48x32.in.f32"), dtype=np.float32).reshape(32, 48, 4)
+    want = np.fromfile(os.path.join(G, "filt_im_48x32.out.f32"), dtype=np.float32).reshape(32, 48, 4)
+    got = po.filt_im(src, 48, 32)
+    assert got.view(np.uint32).tolist() == want.view(np.uint32).tolist()
+    assert int((want[..., 3] == 1).sum()) == 30 * 47 - 1       # rows 1..30 x columns 1..47, minus the pixel whose reads leave the buffer
+
+
+@pytest.mark.skipif(not util.have_ref_cpu(), reason="oracle/_ref/ref_cpu not built (no /root/reference here)")
+def test_filt_im_port_equals_reference_live(tmp_path):
+    rng = np.random.default_rng(3)
+    w, h = 37, 21
+    src = np.zeros((h, w, 4), dtype=np.float32)
+    src[..., :3] = np.round(rng.random((h, w, 3), dtype=np.float32) * 6.0) / 3.0     # coarse values: many equal greys with different colours
+    cin, cout = str(tmp_path / "in.f32"), str(tmp_path / "out.f32")
+    src.tofile(cin)
+    util.run_ref_cpu(w, h, 0, 4, obj=util.CORNELL, want=(), extra=("--colors-in", cin, "--filt-out", cout))
+    want = np.fromfile(cout, dtype=np.float32).reshape(h, w, 4)
+    assert po.filt_im(src, w, h).view(np.uint32).tolist() == want.view(np.uint32).tolist()
