@@ -206,6 +206,22 @@ int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int 
 /* 3x3 median denoise of prog.cl:391-427 as a standalone pass: colors → image (RGBA float). */
 int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height);
 
+/* ---- multi-GPU inside ONE process (SURVEY 8b's ptb_set_gpus; 8e).  After ptb_set_gpus(n, mode) every launch — the reference
+ * host's own gen_ray / trace_ray pairs (main.cpp:683-687) as well as ptb_render — runs on the first n GPUs of the box, counted
+ * from the one ptb_init chose; the host keeps talking to ONE device: all ptb_mem buffers stay on the primary GPU, the others
+ * stage their own copy of the scene (+ LBVH) from the uploaded records through NVLink peer access at their first launch.
+ *   PTB_SPLIT_TILE  GPU d renders the bands of 8 scanlines d, d+n, ... with the reference's per-pixel seeds and stores its pixels'
+ *                   rnds / colors / image straight into the primary's buffers over NVLink (the gather rides on the path kernels'
+ *                   own stores: no collective, no copy).  The frame is bitwise the 1-GPU frame.
+ *   PTB_SPLIT_SPP   sample j of a call goes to GPU (sample index + j) % n (ptb_render(spp) renders spp samples IN TOTAL); every
+ *                   GPU keeps per-pixel sums and its own RNG states (GPU d: state * 16807^(d*W*H) mod 2^31-1, i.e. the host
+ *                   generator's sequence continued), and one kernel on the primary adds the n sums through peer loads, scales
+ *                   and tone-maps (sum -> mean -> image in one pass).  Same expectation as 1 GPU, different random numbers.
+ * n == 1 restores the single-GPU path.  Not combinable with ptb_set_pixel_shard / ptb_set_accumulate_sum / ptb_comm_*. */
+enum { PTB_SPLIT_TILE = 0, PTB_SPLIT_SPP = 1 };
+int ptb_set_gpus(int n, int mode);
+int ptb_get_gpus(void);
+
 /* ---- multi-GPU, one PROCESS per GPU.  The path shards (pixels and samples are independent, the scene is
  * read-only and uploaded by every rank); the one exchange step — the SUM of the ranks' float accumulation buffers at a
  * root — runs over NCCL on the library's stream.  No equivalent in the reference (single device, main.cpp:466,476,506).

@@ -11,6 +11,7 @@ KERNEL_GEN_RAY, KERNEL_TRACE_RAY, KERNEL_FILT_IM = 0, 1, 2
 ACCEL_AUTO, ACCEL_BRUTE, ACCEL_REFBVH, ACCEL_LBVH = 0, 1, 2, 3
 MATH_PARITY, MATH_FAST = 0, 1
 PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_AUTO, PIPE_POOL = 0, 1, 2, 3
+SPLIT_TILE, SPLIT_SPP = 0, 1
 
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py against the header text)
 SYMBOLS = [
@@ -23,6 +24,7 @@ SYMBOLS = [
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
     "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit", "ptb_invalidate", "ptb_resolve_frame", "ptb_save_state", "ptb_load_state",
     "ptb_comm_unique_id", "ptb_comm_init", "ptb_comm_ranks", "ptb_comm_rank", "ptb_comm_reduce", "ptb_comm_broadcast", "ptb_comm_barrier", "ptb_comm_destroy",
+    "ptb_set_gpus", "ptb_get_gpus",
 ]
 
 
@@ -72,6 +74,7 @@ def load_library(path=None):
         "ptb_invalidate": (i, [u64]), "ptb_resolve_frame": (i, [u64, i, i, i, i, u64, vp]),
         "ptb_save_state": (i, [cp]), "ptb_load_state": (i, [cp, C.POINTER(i)]),
         "ptb_comm_unique_id": (i, [vp]), "ptb_comm_init": (i, [i, i, vp]), "ptb_comm_ranks": (i, []), "ptb_comm_rank": (i, []),
+        "ptb_set_gpus": (i, [i, i]), "ptb_get_gpus": (i, []),
         "ptb_comm_reduce": (i, [u64, i]), "ptb_comm_broadcast": (i, [u64, i]), "ptb_comm_barrier": (i, []), "ptb_comm_destroy": (i, []),
     }
     for name, (res, args) in proto.items():
@@ -268,6 +271,10 @@ class Ptb:
         out = np.empty((h, w, 4), dtype=np.uint8) if want_rgba8 else None
         self._ck(self.lib.ptb_resolve_frame(colors, w, h, divide_by, mode, image, out.ctypes.data if want_rgba8 else None), "ptb_resolve_frame")
         return out
+
+    # -- several GPUs inside this process
+    def set_gpus(self, n, mode=0): self._ck(self.lib.ptb_set_gpus(n, mode), "ptb_set_gpus")
+    def get_gpus(self): return self.lib.ptb_get_gpus()
 
     # -- one process per GPU: NCCL behind the boundary
     def comm_unique_id(self):

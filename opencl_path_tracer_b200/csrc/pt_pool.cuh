@@ -305,30 +305,34 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
 // ---------------------------------------------------------------- host side
 struct PoolPlan { int blocks; int total_slots; size_t smem; size_t scratch_bytes; };
 template <bool COUNT, int MODE> static PoolPlan pool_plan_t() {
-    static PoolPlan plan = [] {
-        PoolPlan pl{};
-        int dev = 0, sms = 148, occ = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        pl.smem = (size_t)POOL_WARPS * POOL_WORDS * sizeof(int);
-        if (pl.smem > 48 * 1024) cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
-        cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_pool<COUNT, MODE>, 32 * POOL_WARPS, pl.smem);
-        static const int want = getenv("PTB_POOL_BLOCKS") ? atoi(getenv("PTB_POOL_BLOCKS")) : 0;
-        if (want > 0 && want < occ) occ = want;
-        if (occ < 1) occ = 1;
-        // the carve-out the resident blocks need (+ 1 KB per block the runtime reserves) and nothing more: the rest stays L1 for nodes and triangles
-        int pct = (int)((occ * (pl.smem + sizeof(float4) * WF_BIG_SMEM + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
-        if (pct > 100) pct = 100;
-        cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        pl.blocks = sms * occ;
-        pl.total_slots = pl.blocks * POOL_WARPS * POOL_NS;
-        pl.scratch_bytes = 256 + (size_t)pl.total_slots * POOL_DEEP * sizeof(int2) + 256 + (size_t)pl.total_slots * WF_PLANES * sizeof(float4) + 256;
-        if (getenv("PTB_VERBOSE")) fprintf(stderr, "ptb: k_pool<%d,%d> %d blocks/SM, %zu B smem/block, carve-out %d %%, %d slots, scratch %.1f MB\n",
-                                           (int)COUNT, MODE, occ, pl.smem, pct, pl.total_slots, pl.scratch_bytes / 1048576.0);
-        return pl;
-    }();
-    return plan;
+    static PoolPlan plans[16];
+    static bool have[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 15;
+    if (have[dev]) return plans[dev];            // function attributes are per device: set them once on each
+    PoolPlan pl{};
+    int sms = 148, occ = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    pl.smem = (size_t)POOL_WARPS * POOL_WORDS * sizeof(int);
+    if (pl.smem > 48 * 1024) cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+    cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_pool<COUNT, MODE>, 32 * POOL_WARPS, pl.smem);
+    static const int want = getenv("PTB_POOL_BLOCKS") ? atoi(getenv("PTB_POOL_BLOCKS")) : 0;
+    if (want > 0 && want < occ) occ = want;
+    if (occ < 1) occ = 1;
+    // the carve-out the resident blocks need (+ 1 KB per block the runtime reserves) and nothing more: the rest stays L1 for nodes and triangles
+    int pct = (int)((occ * (pl.smem + sizeof(float4) * WF_BIG_SMEM + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+    if (pct > 100) pct = 100;
+    cudaFuncSetAttribute(k_pool<COUNT, MODE>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    pl.blocks = sms * occ;
+    pl.total_slots = pl.blocks * POOL_WARPS * POOL_NS;
+    pl.scratch_bytes = 256 + (size_t)pl.total_slots * POOL_DEEP * sizeof(int2) + 256 + (size_t)pl.total_slots * WF_PLANES * sizeof(float4) + 256;
+    if (getenv("PTB_VERBOSE")) fprintf(stderr, "ptb: k_pool<%d,%d> on device %d: %d blocks/SM, %zu B smem/block, carve-out %d %%, %d slots, scratch %.1f MB\n",
+                                       (int)COUNT, MODE, dev, occ, pl.smem, pct, pl.total_slots, pl.scratch_bytes / 1048576.0);
+    plans[dev] = pl;
+    have[dev] = true;
+    return pl;
 }
 // bytes of scratch the pool kernels need (the C-ABI allocates them once)
 size_t pool_scratch_bytes() {

@@ -81,9 +81,41 @@ struct PendingGen {                    // a deferred gen_ray launch (ptb_set_fus
     size_t n = 0;
 };
 
+// Everything that lives on ONE GPU.  dev[0] is the primary device (the one ptb_init chose: all ptb_mem buffers live there);
+// dev[1..] exist only in the single-process multi-GPU mode (ptb_set_gpus): they keep their own staged scene + LBVH, scratch and
+// counters, read the uploaded scene through peer access when they stage it, and reach the frame buffers of the primary over NVLink.
+#define PTB_MAX_GPUS 8
+struct DevCtx {
+    int device = -1;
+    cudaStream_t stream = nullptr;     // secondaries only (the primary launches on State::stream)
+    cudaEvent_t ev_done = nullptr;
+    unsigned long long *counters = nullptr;
+    Staged staged;
+    void *wf_blob = nullptr;           // wavefront scratch (ray + path state + queues), grown on demand
+    size_t wf_pixels = 0;
+    void *pool_blob = nullptr;         // scratch of the persistent pool kernel (pt_pool.cuh): cursor, stack overflow, path state
+    size_t pool_bytes = 0;
+    // secondaries: local copy of the materials (one 80-byte gather per hit must not cross NVLink)
+    void *mats = nullptr;
+    size_t mats_bytes = 0;
+    ptb_mem mats_handle = 0;
+    unsigned long long mats_version = ~0ull;
+    // spp split: this device's own RNG states and per-pixel sums
+    int *rnds = nullptr;
+    float4 *sum = nullptr;
+    size_t frame_pixels = 0;
+    ptb_mem rnds_handle = 0;
+    unsigned long long rnds_version = ~0ull;
+    long long sum_index = -1;                          // sample index the sum stands for (-1: not valid)
+    unsigned long long sum_colors_version = ~0ull;     // version of the colors buffer the last resolve wrote
+};
+
 struct State {
     bool inited = false;
     int device = -1;
+    DevCtx dev[PTB_MAX_GPUS];
+    int n_gpus = 1, gpu_mode = PTB_SPLIT_TILE, cur = 0;
+    cudaEvent_t ev_ready = nullptr;
     cudaDeviceProp prop;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     std::map<ptb_mem, MemObj> mems;
@@ -103,19 +135,15 @@ struct State {
     int tex_nodes = 1;                 // node fetches through the texture pipe (PTB_TEX_NODES=0: LSU)
     int wide_bvh = 1;                  // wavefront traversal over the 4-ary collapse of the LBVH (PTB_WIDE_BVH=0: binary)
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
-    unsigned long long *counters = nullptr;
     unsigned long long launches = 0;
-    Staged staged;
     PendingGen pending;
-    void *wf_blob = nullptr;           // wavefront scratch (ray + path state + queues), grown on demand
-    size_t wf_pixels = 0;
-    void *pool_blob = nullptr;         // scratch of the persistent pool kernel (pt_pool.cuh): cursor, stack overflow, path state
-    size_t pool_bytes = 0;
     int auto_pool = 0;                 // PTB_PIPE_AUTO on LBVH scenes: 1 = the pool kernel, 0 = the wavefront (PTB_AUTO_POOL)
 };
 // immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
 // during static destruction, after which ptb_release still gets called
 State &G = *new State();
+inline DevCtx &D() { return G.dev[G.cur]; }                                    // the device the launch path is working on
+inline cudaStream_t S() { return G.cur == 0 ? S() : G.dev[G.cur].stream; }
 
 int fail(int code, const char *fmt, ...) {
     char buf[512];
@@ -195,15 +223,15 @@ int seeds_nonneg(MemObj *rnds, size_t n, bool *out) {
     // one scan per content version: ptb_write / ptb_device_ptr / ptb_invalidate bump it (the owner of wrapped memory calls
     // ptb_invalidate after writing it behind the library's back); the kernels themselves only ever store states in [0, 2^31)
     if (rnds->seeds_version != rnds->version + 1 || rnds->seeds_checked < n) {
-        if (!G.counters) return PTB_SUCCESS;
-        int *flag = reinterpret_cast<int *>(G.counters + PT_CNT_WORDS);      // spare word behind the work counters
-        CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), G.stream));
-        k_any_negative<<<592, 256, 0, G.stream>>>((const int *)rnds->dptr, n, flag);
+        if (!D().counters) return PTB_SUCCESS;
+        int *flag = reinterpret_cast<int *>(D().counters + PT_CNT_WORDS);      // spare word behind the work counters
+        CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), S()));
+        k_any_negative<<<592, 256, 0, S()>>>((const int *)rnds->dptr, n, flag);
         CUDA_OK(cudaGetLastError());
         G.launches++;
         int h = 1;
-        CUDA_OK(cudaMemcpyAsync(&h, flag, sizeof h, cudaMemcpyDeviceToHost, G.stream));
-        CUDA_OK(cudaStreamSynchronize(G.stream));
+        CUDA_OK(cudaMemcpyAsync(&h, flag, sizeof h, cudaMemcpyDeviceToHost, S()));
+        CUDA_OK(cudaStreamSynchronize(S()));
         rnds->seeds_version = rnds->version + 1;
         rnds->seeds_checked = n;
         rnds->seeds_nonneg = h == 0;
@@ -213,7 +241,7 @@ int seeds_nonneg(MemObj *rnds, size_t n, bool *out) {
 }
 
 int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
-    Staged &s = G.staged;
+    Staged &s = D().staged;
     if (s.tris_handle == handle && s.tris_version == tris->version && s.n_tris == n_tris) return PTB_SUCCESS;
     if ((size_t)n_tris * sizeof(RefTriangle) > tris->bytes)
         return fail(PTB_ERR_INVALID_ARGS, "trace_ray: tris_size %d exceeds the triangle buffer (%zu bytes)", n_tris, tris->bytes);
@@ -235,13 +263,13 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
     s.max_mati = 0;
     if (n_tris > 0) {
         // largest material index of the upload, behind the work counters (next to the seed-scan flag)
-        unsigned *max_mati = reinterpret_cast<unsigned *>(G.counters + PT_CNT_WORDS + 1);
-        CUDA_OK(cudaMemsetAsync(max_mati, 0, sizeof(unsigned), G.stream));
-        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, G.stream>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.mati, max_mati);
+        unsigned *max_mati = reinterpret_cast<unsigned *>(D().counters + PT_CNT_WORDS + 1);
+        CUDA_OK(cudaMemsetAsync(max_mati, 0, sizeof(unsigned), S()));
+        k_stage_tris<<<(n_tris + 255) / 256, 256, 0, S()>>>((const RefTriangle *)tris->dptr, n_tris, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.mati, max_mati);
         CUDA_OK(cudaGetLastError());
         G.launches++;
-        CUDA_OK(cudaMemcpyAsync(&s.max_mati, max_mati, sizeof(unsigned), cudaMemcpyDeviceToHost, G.stream));
-        CUDA_OK(cudaStreamSynchronize(G.stream));
+        CUDA_OK(cudaMemcpyAsync(&s.max_mati, max_mati, sizeof(unsigned), cudaMemcpyDeviceToHost, S()));
+        CUDA_OK(cudaStreamSynchronize(S()));
     }
     s.tris_handle = handle;
     s.tris_version = tris->version;
@@ -254,7 +282,7 @@ int stage_scene(MemObj *tris, ptb_mem handle, int n_tris) {
 // Merge coplanar same-material triangle pairs into convex quads for the fast shared-memory scan (prims.cu).
 // Leaves n_prims = 0 when nothing merges, so the launch keeps the plain triangle scan.
 int ensure_prims() {
-    Staged &s = G.staged;
+    Staged &s = D().staged;
     if (s.prims_valid) return PTB_SUCCESS;
     s.n_prims = 0;
     s.prims_valid = true;
@@ -268,12 +296,12 @@ int ensure_prims() {
         CUDA_OK(cudaMalloc((void **)&s.prim_rep, PRIMS_MAX_TRIS * sizeof(int)));
         CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
     }
-    prims_build(s.q0, s.q1, s.q2, s.mati, nullptr, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.prim_shade, s.n_prims_dev, G.stream);
+    prims_build(s.q0, s.q1, s.q2, s.mati, nullptr, s.n_tris, s.p0, s.p1, s.p2, s.prim_ab, s.prim_rep, s.prim_shade, s.n_prims_dev, S());
     CUDA_OK(cudaGetLastError());
     G.launches++;
     int n = 0;
-    CUDA_OK(cudaMemcpyAsync(&n, s.n_prims_dev, sizeof n, cudaMemcpyDeviceToHost, G.stream));
-    CUDA_OK(cudaStreamSynchronize(G.stream));
+    CUDA_OK(cudaMemcpyAsync(&n, s.n_prims_dev, sizeof n, cudaMemcpyDeviceToHost, S()));
+    CUDA_OK(cudaStreamSynchronize(S()));
     if (n > 0 && n < s.n_tris) s.n_prims = n;
     return PTB_SUCCESS;
 }
@@ -286,12 +314,12 @@ int resolve_accel(int n_tris, bool have_tree) {
 }
 
 int ensure_lbvh(float reach) {
-    Staged &s = G.staged;
+    Staged &s = D().staged;
     char err[256];
     err[0] = 0;
     if (!s.lbvh_valid || s.lbvh_leaf != G.lbvh_leaf) {
         unsigned long long before = s.lbvh.launches;
-        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.n_tris, G.lbvh_leaf, G.lbvh_big, G.stream, err, sizeof err))
+        if (lbvh_build(&s.lbvh, s.q0, s.q1, s.q2, s.f0, s.f1, s.f2, s.n_tris, G.lbvh_leaf, G.lbvh_big, S(), err, sizeof err))
             return fail(PTB_ERR_DEVICE, "%s", err);
         G.launches += s.lbvh.launches - before + 4;   // + the radix-sort passes
         s.lbvh_valid = true;
@@ -309,19 +337,19 @@ int ensure_lbvh(float reach) {
             if (!s.n_prims_dev) CUDA_OK(cudaMalloc((void **)&s.n_prims_dev, sizeof(int)));
             const int first = s.lbvh.n_tree;
             prims_build(s.lbvh.sq0 + first, s.lbvh.sq1 + first, s.lbvh.sq2 + first, s.mati, s.lbvh.sorted_id + first, s.lbvh.n_big,
-                        s.b0, s.b1, s.b2, s.big_ab, s.big_rep, s.big_shade, s.n_prims_dev, G.stream);
+                        s.b0, s.b1, s.b2, s.big_ab, s.big_rep, s.big_shade, s.n_prims_dev, S());
             CUDA_OK(cudaGetLastError());
             G.launches++;
             int nb = 0;
-            CUDA_OK(cudaMemcpyAsync(&nb, s.n_prims_dev, sizeof nb, cudaMemcpyDeviceToHost, G.stream));
-            CUDA_OK(cudaStreamSynchronize(G.stream));
+            CUDA_OK(cudaMemcpyAsync(&nb, s.n_prims_dev, sizeof nb, cudaMemcpyDeviceToHost, S()));
+            CUDA_OK(cudaStreamSynchronize(S()));
             s.n_big_prims = nb > 0 ? nb : 0;
         }
         if (s.lbvh.max_depth > 62)
             return fail(PTB_ERR_DEVICE, "lbvh: tree depth %d exceeds the traversal stack", s.lbvh.max_depth);
     }
     if (reach > 4.0f * s.lbvh.reach) {   // camera far outside the scene: widen the boxes (cheap re-emit)
-        if (lbvh_emit(&s.lbvh, reach, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+        if (lbvh_emit(&s.lbvh, reach, S(), err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
         G.launches++;
     }
     return PTB_SUCCESS;
@@ -350,7 +378,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     if (tris_size < 0) tris_size = 0;
     int rc = stage_scene(tris, G.args[K][1].mem, tris_size);
     if (rc) return rc;
-    Staged &s = G.staged;
+    Staged &s = D().staged;
     bool have_tree = tree && shift && shift_size > 0 && shift->bytes >= (size_t)shift_size * 4;
     p.accel = resolve_accel(tris_size, have_tree);
     const bool fastm = G.math == PTB_MATH_FAST;   // each arithmetic flavour reads its own triangle layout
@@ -403,7 +431,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.shard_rank = G.shard_rank; p.shard_n = G.shard_n; p.shard_group = G.shard_group;
     p.sum_mode = G.sum_mode;
     p.count_work = G.count_work;
-    p.counters = G.counters;
+    p.counters = D().counters;
     if (fastm && !from_rays) {                       // (a two-kernel host may hand trace_ray states gen_ray never saw)
         bool ok_seeds = false;
         rc = seeds_nonneg(rnds, npix, &ok_seeds);
@@ -414,7 +442,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     return PTB_SUCCESS;
 }
 
-int run_gen_ray(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n) {
+int run_gen_ray_one(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n, int shard_rank, int shard_n, int shard_group) {
     MemObj *rays = find(rays_h), *rnds = find(rnds_h);
     if (!rays || !rnds) return fail(PTB_ERR_INVALID_ARGS, "gen_ray: buffer argument 0 or 2 is not set");
     if (rays->bytes < n * 32 || rnds->bytes < n * 4) return fail(PTB_ERR_INVALID_ARGS, "gen_ray: rays/rnds smaller than the launch (%zu)", n);
@@ -424,12 +452,44 @@ int run_gen_ray(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n) 
     pt_cam_affine(p);
     p.rays = (RefRay *)rays->dptr;
     p.rnds = (int *)rnds->dptr;
-    p.shard_rank = G.shard_rank; p.shard_n = G.shard_n; p.shard_group = G.shard_group;
-    if (G.math == PTB_MATH_PARITY) pt_parity::launch_gen_ray(p, n, G.stream);
-    else pt_fast::launch_gen_ray(p, n, G.stream);
+    p.shard_rank = shard_rank; p.shard_n = shard_n; p.shard_group = shard_group;
+    if (G.math == PTB_MATH_PARITY) pt_parity::launch_gen_ray(p, n, S());
+    else pt_fast::launch_gen_ray(p, n, S());
     CUDA_OK(cudaGetLastError());
     G.launches++;
     return PTB_SUCCESS;
+}
+
+// switch the launch path to device index i of the single-process multi-GPU mode (and back when the scope ends)
+struct DevScope {
+    int prev;
+    explicit DevScope(int i) : prev(G.cur) { G.cur = i; cudaSetDevice(G.dev[i].device); }
+    ~DevScope() { G.cur = prev; cudaSetDevice(G.dev[prev].device); }
+};
+int multi_fork() {          // the secondaries' streams continue after everything enqueued on the primary's so far
+    if (!G.ev_ready) CUDA_OK(cudaEventCreateWithFlags(&G.ev_ready, cudaEventDisableTiming));
+    CUDA_OK(cudaEventRecord(G.ev_ready, G.stream));
+    for (int d = 1; d < G.n_gpus; ++d) CUDA_OK(cudaStreamWaitEvent(G.dev[d].stream, G.ev_ready, 0));
+    return PTB_SUCCESS;
+}
+int multi_join() {          // ... and the primary's stream after everything the secondaries were given
+    for (int d = 1; d < G.n_gpus; ++d) {
+        DevScope scope(d);
+        CUDA_OK(cudaEventRecord(D().ev_done, D().stream));
+    }
+    for (int d = 1; d < G.n_gpus; ++d) CUDA_OK(cudaStreamWaitEvent(G.stream, G.dev[d].ev_done, 0));
+    return PTB_SUCCESS;
+}
+int run_gen_ray(ptb_mem rays_h, ptb_mem rnds_h, const RefCamera &cam, size_t n) {
+    if (G.n_gpus <= 1) return run_gen_ray_one(rays_h, rnds_h, cam, n, G.shard_rank, G.shard_n, G.shard_group);
+    if (G.gpu_mode != PTB_SPLIT_TILE) return fail(PTB_ERR_INVALID_VALUE, "gen_ray as its own launch needs the tile split (the spp split renders through the fused launch or ptb_render)");
+    int rc = multi_fork();
+    const int group = 8 * (int)cam.XM > 0 ? 8 * (int)cam.XM : 8;
+    for (int d = 0; d < G.n_gpus && !rc; ++d) {
+        DevScope scope(d);
+        rc = run_gen_ray_one(rays_h, rnds_h, cam, n, d, G.n_gpus, group);
+    }
+    return rc ? rc : multi_join();
 }
 
 int flush_pending() {
@@ -439,8 +499,8 @@ int flush_pending() {
 }
 
 int run_render(const RenderParams &p) {
-    if (G.math == PTB_MATH_PARITY) pt_parity::launch_render(p, G.stream);
-    else pt_fast::launch_render(p, G.stream);
+    if (G.math == PTB_MATH_PARITY) pt_parity::launch_render(p, S());
+    else pt_fast::launch_render(p, S());
     CUDA_OK(cudaGetLastError());
     G.launches++;
     return PTB_SUCCESS;
@@ -451,20 +511,20 @@ int run_render(const RenderParams &p) {
 #define WF_QUEUE_SLACK 8192
 int run_wavefront(RenderParams &p) {
     const size_t n = (size_t)p.W * p.H;
-    if (n > G.wf_pixels) {
-        cudaFree(G.wf_blob);
-        G.wf_blob = nullptr; G.wf_pixels = 0;
-        CUDA_OK(cudaMalloc(&G.wf_blob, n * 136 + 2 * WF_QUEUE_SLACK + 256));
-        G.wf_pixels = n;
+    if (n > D().wf_pixels) {
+        cudaFree(D().wf_blob);
+        D().wf_blob = nullptr; D().wf_pixels = 0;
+        CUDA_OK(cudaMalloc(&D().wf_blob, n * 136 + 2 * WF_QUEUE_SLACK + 256));
+        D().wf_pixels = n;
     }
-    char *b = (char *)G.wf_blob;
+    char *b = (char *)D().wf_blob;
     p.wf_ray0 = (float4 *)b; b += n * 16;
     p.wf_ray1 = (float4 *)b; b += n * 16;
     p.wf_state = (float4 *)b; b += n * 96;
     p.wf_queue[0] = (int *)b; b += n * 4 + WF_QUEUE_SLACK;
     p.wf_queue[1] = (int *)b; b += n * 4 + WF_QUEUE_SLACK;
     p.wf_ctrl = (int *)b;
-    int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_wavefront(p, G.stream) : pt_fast::launch_wavefront(p, G.stream);
+    int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_wavefront(p, S()) : pt_fast::launch_wavefront(p, S());
     CUDA_OK(cudaGetLastError());
     G.launches += (unsigned long long)k;
     return PTB_SUCCESS;
@@ -478,21 +538,154 @@ bool want_pool(const RenderParams &p) {
 }
 int ensure_pool_blob() {
     const size_t need = G.math == PTB_MATH_PARITY ? pt_parity::pool_scratch_bytes() : pt_fast::pool_scratch_bytes();
-    if (need > G.pool_bytes) {
-        cudaFree(G.pool_blob);
-        G.pool_blob = nullptr; G.pool_bytes = 0;
-        CUDA_OK(cudaMalloc(&G.pool_blob, need));
-        G.pool_bytes = need;
+    if (need > D().pool_bytes) {
+        cudaFree(D().pool_blob);
+        D().pool_blob = nullptr; D().pool_bytes = 0;
+        CUDA_OK(cudaMalloc(&D().pool_blob, need));
+        D().pool_bytes = need;
     }
     return PTB_SUCCESS;
 }
 int run_pool(const RenderParams &p) {
     int rc = ensure_pool_blob();
     if (rc) return rc;
-    const int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool(p, G.pool_blob, G.stream) : pt_fast::launch_pool(p, G.pool_blob, G.stream);
+    const int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool(p, D().pool_blob, S()) : pt_fast::launch_pool(p, D().pool_blob, S());
     CUDA_OK(cudaGetLastError());
     G.launches += (unsigned long long)k;
     return PTB_SUCCESS;
+}
+
+// which kernels render this launch
+int run_any(RenderParams &p, bool allow_wavefront) {
+    if (want_pool(p)) return run_pool(p);
+    if (!p.from_rays && p.spp >= 1 && allow_wavefront && G.pipe != PTB_PIPE_MEGAKERNEL && G.pipe != PTB_PIPE_POOL && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);
+    return run_render(p);
+}
+
+// seeds of GPU d > 0 under the spp split: state_d = state_0 * 16807^(d * W * H) mod (2^31 - 1) — for a freshly seeded buffer that is
+// the host generator's sequence continued (pixel i of GPU d gets output i + d*W*H of std::minstd_rand0, main.cpp:522-526 carried on)
+__global__ void k_derive_seeds(const int *src, int *dst, size_t n, unsigned long long mult) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long s = (unsigned long long)(unsigned)src[i] % 2147483647ull;
+    if (s == 0) s = 1;
+    dst[i] = (int)((s * mult) % 2147483647ull);
+}
+unsigned long long powmod(unsigned long long b, unsigned long long e) {
+    const unsigned long long M = 2147483647ull;
+    unsigned long long r = 1;
+    b %= M;
+    while (e) { if (e & 1) r = r * b % M; b = b * b % M; e >>= 1; }
+    return r;
+}
+
+// ONE render call on every GPU of the single-process multi-GPU mode (ptb_set_gpus).
+//   tile: GPU d renders the bands of 8 scanlines d, d+n, ... with the reference's seeds; rnds / colors / tex are the PRIMARY's buffers,
+//         reached by the other GPUs' kernels over NVLink (peer access): the gather rides on the kernels' own end-of-pixel stores.
+//         Bitwise the 1-GPU image.
+//   spp:  sample j of the call goes to GPU (sample0 + j) % n; every GPU keeps its own RNG states (derived, see above) and a
+//         per-pixel SUM on its own HBM; afterwards ONE kernel on the primary adds the n sums through peer loads, scales by
+//         1 / total samples and writes the mean into colors and the tone-mapped image (the fused root resolve, no NCCL).
+int render_multi(size_t W, size_t H, int spp, bool from_rays) {
+    const int K = PTB_KERNEL_TRACE_RAY, n = G.n_gpus;
+    const bool spp_mode = G.gpu_mode == PTB_SPLIT_SPP;
+    if (G.shard_n > 1) return fail(PTB_ERR_INVALID_VALUE, "ptb_set_pixel_shard and ptb_set_gpus do not combine");
+    if (spp_mode && (from_rays || G.sum_mode)) return fail(PTB_ERR_INVALID_VALUE, "the spp split needs the fused launch (or ptb_render) and the running-mean accumulation");
+    bool ok = true;
+    const int sample0 = arg_val<int>(K, 10, &ok);
+    MemObj *rnds = arg_mem(K, 8), *colors = arg_mem(K, 12), *tex = arg_mem(K, 0);
+    if (!ok || !rnds || !colors) return fail(PTB_ERR_INVALID_ARGS, "trace_ray: arguments 8, 10, 12 are not set");
+    const size_t npix = W * H;
+    int rc = multi_fork();
+    if (rc) return rc;
+    for (int d = 0; d < n; ++d) {
+        DevScope scope(d);
+        DevCtx &c = D();
+        int spp_d = spp;
+        if (spp_mode) {
+            const int first = (((d - sample0) % n) + n) % n;          // first j with (sample0 + j) % n == d
+            spp_d = first < spp ? (spp - first + n - 1) / n : 0;
+        }
+        RenderParams p;
+        rc = make_params(p, W, H, spp_d > 0 ? spp_d : 1, from_rays);
+        if (rc) return rc;
+        if (d > 0) {                                                  // materials: a local copy (an 80-byte gather per hit must not cross NVLink)
+            MemObj *mats = arg_mem(K, 3);
+            if (c.mats_handle != G.args[K][3].mem || c.mats_version != mats->version || c.mats_bytes < mats->bytes) {
+                if (c.mats_bytes < mats->bytes) {
+                    cudaFree(c.mats); c.mats = nullptr; c.mats_bytes = 0;
+                    CUDA_OK(cudaMalloc(&c.mats, mats->bytes ? mats->bytes : 1));
+                    c.mats_bytes = mats->bytes;
+                }
+                CUDA_OK(cudaMemcpyPeerAsync(c.mats, c.device, mats->dptr, G.device, mats->bytes, S()));
+                c.mats_handle = G.args[K][3].mem; c.mats_version = mats->version;
+            }
+            p.sc.mats = (const RefMaterial *)c.mats;
+        }
+        if (spp_mode) {
+            if (c.frame_pixels < npix) {
+                cudaFree(c.rnds); cudaFree(c.sum);
+                c.rnds = nullptr; c.sum = nullptr; c.frame_pixels = 0; c.rnds_version = ~0ull; c.sum_index = -1;
+                if (d > 0) CUDA_OK(cudaMalloc((void **)&c.rnds, npix * sizeof(int)));
+                CUDA_OK(cudaMalloc((void **)&c.sum, npix * sizeof(float4)));
+                c.frame_pixels = npix;
+            }
+            if (d > 0 && (c.rnds_handle != G.args[K][8].mem || c.rnds_version != rnds->version)) {
+                k_derive_seeds<<<(unsigned)((npix + 255) / 256), 256, 0, S()>>>((const int *)rnds->dptr, c.rnds, npix, powmod(16807ull, (unsigned long long)d * npix));
+                CUDA_OK(cudaGetLastError());
+                G.launches++;
+                c.rnds_handle = G.args[K][8].mem; c.rnds_version = rnds->version;
+            }
+            // the sums are a cache of "colors x samples so far": rebuilt when the host moved the sample index or rewrote colors (checkpoint resume)
+            if (sample0 == 0 || c.sum_index != sample0 || c.sum_colors_version != colors->version) {
+                if (sample0 != 0 && d == 0) {
+                    ResolveSrc src{};
+                    src.p[0] = (const float4 *)colors->dptr; src.n = 1;
+                    resolve_frame(src, (float)sample0, (int)npix, 1, 0, c.sum, nullptr, nullptr, S());
+                    G.launches++;
+                } else CUDA_OK(cudaMemsetAsync(c.sum, 0, npix * sizeof(float4), S()));
+            }
+            c.sum_index = sample0 + spp;
+            if (d > 0) p.rnds = c.rnds;
+            p.colors = c.sum; p.sum_mode = 1; p.tex = nullptr;
+        } else {
+            p.shard_rank = d; p.shard_n = n; p.shard_group = 8 * (int)W;
+        }
+        if (spp_d > 0) {
+            rc = run_any(p, false);                                    // never the host-looped wavefront here: the GPUs must run concurrently
+            if (rc) return rc;
+        }
+    }
+    rc = multi_join();
+    if (rc) return rc;
+    if (spp_mode) {
+        ResolveSrc src{};
+        for (int d = 0; d < n; ++d) src.p[d] = G.dev[d].sum;
+        src.n = n;
+        const bool tex_ok = tex && tex->bytes >= npix * 16;
+        resolve_frame(src, 1.0f / (float)(sample0 + spp), (int)W, (int)H, 0, (float4 *)colors->dptr, tex_ok ? (float4 *)tex->dptr : nullptr, nullptr, G.stream);
+        CUDA_OK(cudaGetLastError());
+        G.launches++;
+        for (int d = 0; d < n; ++d) G.dev[d].sum_colors_version = colors->version;
+    }
+    return PTB_SUCCESS;
+}
+
+void free_dev(DevCtx &c) {
+    Staged &s = c.staged;
+    cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
+    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_shade); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
+    cudaFree(s.b0); cudaFree(s.b1); cudaFree(s.b2); cudaFree(s.big_ab); cudaFree(s.big_shade); cudaFree(s.big_rep);
+    lbvh_free(&s.lbvh);
+    s = Staged();
+    cudaFree(c.counters); c.counters = nullptr;
+    cudaFree(c.wf_blob); c.wf_blob = nullptr; c.wf_pixels = 0;
+    cudaFree(c.pool_blob); c.pool_blob = nullptr; c.pool_bytes = 0;
+    cudaFree(c.mats); c.mats = nullptr; c.mats_bytes = 0; c.mats_handle = 0;
+    cudaFree(c.rnds); cudaFree(c.sum); c.rnds = nullptr; c.sum = nullptr; c.frame_pixels = 0; c.rnds_handle = 0; c.sum_index = -1;
+    if (c.stream) cudaStreamDestroy(c.stream);
+    if (c.ev_done) cudaEventDestroy(c.ev_done);
+    c.stream = nullptr; c.ev_done = nullptr;
 }
 
 }  // namespace
@@ -516,9 +709,11 @@ int ptb_init(int device_ordinal) {
     CUDA_OK(cudaGetDeviceProperties(&G.prop, dev));
     CUDA_OK(cudaStreamCreateWithFlags(&G.own_stream, cudaStreamNonBlocking));
     G.stream = G.own_stream;
-    CUDA_OK(cudaMalloc((void **)&G.counters, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
-    CUDA_OK(cudaMemset(G.counters, 0, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
+    CUDA_OK(cudaMalloc((void **)&D().counters, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
+    CUDA_OK(cudaMemset(D().counters, 0, (PT_CNT_WORDS + 2) * sizeof(unsigned long long)));
     G.device = dev;
+    G.dev[0].device = dev;
+    G.cur = 0; G.n_gpus = 1;
     G.inited = true;
     const char *env;
     if ((env = getenv("PTB_MATH"))) G.math = atoi(env) ? PTB_MATH_FAST : PTB_MATH_PARITY;
@@ -539,25 +734,24 @@ int ptb_init(int device_ordinal) {
 int ptb_shutdown(void) {
     if (!G.inited) return PTB_SUCCESS;
     cudaSetDevice(G.device);
-    cudaStreamSynchronize(G.stream);
+    cudaStreamSynchronize(S());
     comm_destroy();
     for (auto &kv : G.mems) {
         if (kv.second.owned) cudaFree(kv.second.dptr);
         else if (kv.second.ipc) cudaIpcCloseMemHandle(kv.second.dptr);
     }
     G.mems.clear();
-    Staged &s = G.staged;
-    cudaFree(s.q0); cudaFree(s.q1); cudaFree(s.q2); cudaFree(s.f0); cudaFree(s.f1); cudaFree(s.f2); cudaFree(s.mati);
-    cudaFree(s.p0); cudaFree(s.p1); cudaFree(s.p2); cudaFree(s.prim_ab); cudaFree(s.prim_shade); cudaFree(s.prim_rep); cudaFree(s.n_prims_dev);
-    cudaFree(s.b0); cudaFree(s.b1); cudaFree(s.b2); cudaFree(s.big_ab); cudaFree(s.big_shade); cudaFree(s.big_rep);
-    lbvh_free(&s.lbvh);
-    s = Staged();
-    cudaFree(G.counters);
-    G.counters = nullptr;
-    cudaFree(G.wf_blob);
-    G.wf_blob = nullptr; G.wf_pixels = 0;
-    cudaFree(G.pool_blob);
-    G.pool_blob = nullptr; G.pool_bytes = 0;
+    for (int d = G.n_gpus - 1; d >= 0; --d) {
+        if (G.dev[d].device < 0) continue;
+        cudaSetDevice(G.dev[d].device);
+        if (d > 0 && G.dev[d].stream) cudaStreamSynchronize(G.dev[d].stream);
+        free_dev(G.dev[d]);
+        if (d > 0) G.dev[d].device = -1;
+    }
+    for (int d = 1; d < PTB_MAX_GPUS; ++d) G.dev[d] = DevCtx();
+    G.n_gpus = 1; G.cur = 0;
+    cudaSetDevice(G.device);
+    if (G.ev_ready) { cudaEventDestroy(G.ev_ready); G.ev_ready = nullptr; }
     cudaStreamDestroy(G.own_stream);
     G.own_stream = G.stream = nullptr;
     for (auto &k : G.args) for (auto &a : k) a = Arg();
@@ -595,7 +789,7 @@ ptb_mem ptb_alloc(size_t bytes) {
     m.bytes = bytes;
     cudaError_t e = cudaMalloc(&m.dptr, bytes ? bytes : 1);
     if (e != cudaSuccess) { fail(PTB_ERR_OUT_OF_MEMORY, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); return 0; }
-    cudaMemsetAsync(m.dptr, 0, bytes, G.stream);
+    cudaMemsetAsync(m.dptr, 0, bytes, S());
     ptb_mem h = G.next++;
     G.mems[h] = m;
     return h;
@@ -619,10 +813,14 @@ int ptb_release(ptb_mem h) {
     if (--m->refs == 0) {
         if (G.inited) {
             if (G.pending.active && (G.pending.rays == h || G.pending.rnds == h)) G.pending.active = false;
-            if (m->owned) { cudaStreamSynchronize(G.stream); cudaFree(m->dptr); }
-            else if (m->ipc) { cudaStreamSynchronize(G.stream); cudaIpcCloseMemHandle(m->dptr); }
+            if (m->owned) { cudaStreamSynchronize(S()); cudaFree(m->dptr); }
+            else if (m->ipc) { cudaStreamSynchronize(S()); cudaIpcCloseMemHandle(m->dptr); }
         }
-        if (G.staged.tris_handle == h) G.staged.tris_handle = 0;
+        for (auto &c : G.dev) {
+            if (c.staged.tris_handle == h) c.staged.tris_handle = 0;
+            if (c.mats_handle == h) c.mats_handle = 0;
+            if (c.rnds_handle == h) c.rnds_handle = 0;
+        }
         G.mems.erase(h);
     }
     return PTB_SUCCESS;
@@ -635,8 +833,8 @@ int ptb_write(ptb_mem h, size_t off, size_t bytes, const void *src) {
     if (!src || off > m->bytes || bytes > m->bytes - off) return fail(PTB_ERR_INVALID_VALUE, "ptb_write: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
     int rc = flush_pending();
     if (rc) return rc;
-    CUDA_OK(cudaMemcpyAsync((char *)m->dptr + off, src, bytes, cudaMemcpyHostToDevice, G.stream));
-    CUDA_OK(cudaStreamSynchronize(G.stream));
+    CUDA_OK(cudaMemcpyAsync((char *)m->dptr + off, src, bytes, cudaMemcpyHostToDevice, S()));
+    CUDA_OK(cudaStreamSynchronize(S()));
     m->version++;
     return PTB_SUCCESS;
 }
@@ -648,8 +846,8 @@ int ptb_read(ptb_mem h, size_t off, size_t bytes, void *dst) {
     if (!dst || off > m->bytes || bytes > m->bytes - off) return fail(PTB_ERR_INVALID_VALUE, "ptb_read: range [%zu,%zu) outside a %zu-byte buffer", off, off + bytes, m->bytes);
     int rc = flush_pending();
     if (rc) return rc;
-    CUDA_OK(cudaMemcpyAsync(dst, (const char *)m->dptr + off, bytes, cudaMemcpyDeviceToHost, G.stream));
-    CUDA_OK(cudaStreamSynchronize(G.stream));
+    CUDA_OK(cudaMemcpyAsync(dst, (const char *)m->dptr + off, bytes, cudaMemcpyDeviceToHost, S()));
+    CUDA_OK(cudaStreamSynchronize(S()));
     return PTB_SUCCESS;
 }
 int ptb_ingest_mesh(ptb_mem tris_h, size_t first_tri, const float *vertices, size_t n_verts, const int *indices,
@@ -681,15 +879,15 @@ int ptb_ingest_mesh(ptb_mem tris_h, size_t first_tri, const float *vertices, siz
     cudaError_t e = cudaMalloc((void **)&dv, vb);
     if (e == cudaSuccess) e = cudaMalloc((void **)&di, ib);
     if (e == cudaSuccess) e = cudaMalloc((void **)&dm, mb);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, vertices, vb, cudaMemcpyHostToDevice, G.stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(di, indices, ib, cudaMemcpyHostToDevice, G.stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(dm, mat_ids, mb, cudaMemcpyHostToDevice, G.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dv, vertices, vb, cudaMemcpyHostToDevice, S());
+    if (e == cudaSuccess) e = cudaMemcpyAsync(di, indices, ib, cudaMemcpyHostToDevice, S());
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dm, mat_ids, mb, cudaMemcpyHostToDevice, S());
     if (e == cudaSuccess) {
-        ingest_launch(dv, di, dm, n_faces, x, (RefTriangle *)m->dptr + first_tri, G.stream);
+        ingest_launch(dv, di, dm, n_faces, x, (RefTriangle *)m->dptr + first_tri, S());
         e = cudaGetLastError();
         G.launches++;
     }
-    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(S());
     cudaFree(dv); cudaFree(di); cudaFree(dm);
     if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_ingest_mesh: %s", cudaGetErrorString(e));
     m->version++;
@@ -811,11 +1009,11 @@ int ptb_launch(int k, size_t gx, size_t gy) {
             if (fused) G.pending.active = false;
             else { int rc = flush_pending(); if (rc) return rc; }
         }
+        if (G.n_gpus > 1) return render_multi(gx, gy, 1, !fused);
         RenderParams p;
         int rc = make_params(p, gx, gy, 1, !fused);
         if (rc) return rc;
-        if (want_pool(p)) return run_pool(p);
-        return run_render(p);
+        return run_any(p, false);            // single-sample launches: the pool kernel or the megakernel
     }
     if (k == PTB_KERNEL_FILT_IM) {
         // filt_im(tex, colors) — prog.cl:391-427; launched over (W,H) (main.cpp:665-668, commented out there)
@@ -830,7 +1028,7 @@ int ptb_finish(void) {
     NEED_INIT();
     int rc = flush_pending();
     if (rc) return rc;
-    CUDA_OK(cudaStreamSynchronize(G.stream));
+    CUDA_OK(cudaStreamSynchronize(S()));
     return PTB_SUCCESS;
 }
 const char *ptb_last_error(void) { return G.err.c_str(); }
@@ -864,14 +1062,14 @@ int ptb_set_fuse_gen(int on) {
 }
 int ptb_set_merge_prims(int on) {
     G.merge_prims = on ? 1 : 0;
-    G.staged.prims_valid = false;
+    for (auto &c : G.dev) c.staged.prims_valid = false;
     return PTB_SUCCESS;
 }
 int ptb_set_parity_filter(int on) {
     G.parity_filter = on ? 1 : 0;
     return PTB_SUCCESS;
 }
-int ptb_scan_prims(void) { return G.staged.prims_valid && G.staged.n_prims > 0 ? G.staged.n_prims : (G.staged.n_tris > 0 ? G.staged.n_tris : 0); }
+int ptb_scan_prims(void) { return D().staged.prims_valid && D().staged.n_prims > 0 ? D().staged.n_prims : (D().staged.n_tris > 0 ? D().staged.n_tris : 0); }
 int ptb_set_lbvh_leaf(int max_tris) {
     if (max_tris < 1 || max_tris > 8) return PTB_ERR_INVALID_VALUE;
     G.lbvh_leaf = max_tris;
@@ -892,16 +1090,61 @@ int ptb_build_accel(void) {
     bool ok = true;
     int n = arg_val<int>(K, 2, &ok);
     if (!tris || !ok) return PTB_SUCCESS;   // nothing uploaded yet: the first launch will build
-    int rc = stage_scene(tris, G.args[K][1].mem, n < 0 ? 0 : n);
-    if (rc) return rc;
     int ns = arg_val<int>(K, 6, &ok);
-    if (resolve_accel(n, arg_mem(K, 4) && arg_mem(K, 5) && ns > 0) == PT_ACCEL_LBVH) {
-        rc = ensure_lbvh(0.0f);
+    const bool lbvh = resolve_accel(n, arg_mem(K, 4) && arg_mem(K, 5) && ns > 0) == PT_ACCEL_LBVH;
+    for (int d = 0; d < G.n_gpus; ++d) {
+        DevScope scope(d);
+        int rc = stage_scene(tris, G.args[K][1].mem, n < 0 ? 0 : n);
         if (rc) return rc;
+        if (lbvh) {
+            rc = ensure_lbvh(0.0f);
+            if (rc) return rc;
+        }
+        CUDA_OK(cudaStreamSynchronize(S()));
     }
-    CUDA_OK(cudaStreamSynchronize(G.stream));
     return PTB_SUCCESS;
 }
+
+// Single-process multi-GPU (SURVEY 8b's ptb_set_gpus): the next launches run on the first n GPUs of the box, counted from the
+// one ptb_init chose.  See render_multi above for what each mode does.
+int ptb_set_gpus(int n, int mode) {
+    NEED_INIT();
+    if (mode != PTB_SPLIT_TILE && mode != PTB_SPLIT_SPP) return fail(PTB_ERR_INVALID_VALUE, "ptb_set_gpus: mode must be PTB_SPLIT_TILE or PTB_SPLIT_SPP");
+    int count = 0;
+    CUDA_OK(cudaGetDeviceCount(&count));
+    if (n < 1 || n > PTB_MAX_GPUS || n > count) return fail(PTB_ERR_INVALID_VALUE, "ptb_set_gpus: %d GPUs requested, %d present (at most %d)", n, count, PTB_MAX_GPUS);
+    int rc = flush_pending();
+    if (rc) return rc;
+    CUDA_OK(cudaStreamSynchronize(G.stream));
+    for (int d = 1; d < n; ++d) {
+        DevCtx &c = G.dev[d];
+        if (c.device >= 0) continue;
+        const int dev = (G.device + d) % count;
+        int a = 0, b = 0;
+        CUDA_OK(cudaDeviceCanAccessPeer(&a, dev, G.device));
+        CUDA_OK(cudaDeviceCanAccessPeer(&b, G.device, dev));
+        if (!a || !b) return fail(PTB_ERR_DEVICE, "ptb_set_gpus: no peer access between GPU %d and GPU %d", G.device, dev);
+        cudaError_t e = cudaDeviceEnablePeerAccess(dev, 0);                     // primary -> dev (the spp split's resolve reads the peers' sums)
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(PTB_ERR_DEVICE, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        CUDA_OK(cudaSetDevice(dev));
+        e = cudaDeviceEnablePeerAccess(G.device, 0);                            // dev -> primary (scene staging reads, frame stores)
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { cudaSetDevice(G.device); return fail(PTB_ERR_DEVICE, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e)); }
+        cudaGetLastError();
+        e = cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c.ev_done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&c.counters, (PT_CNT_WORDS + 2) * sizeof(unsigned long long));
+        if (e == cudaSuccess) e = cudaMemset(c.counters, 0, (PT_CNT_WORDS + 2) * sizeof(unsigned long long));
+        cudaSetDevice(G.device);
+        if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_set_gpus: GPU %d: %s", dev, cudaGetErrorString(e));
+        c.device = dev;
+    }
+    G.n_gpus = n;
+    G.gpu_mode = mode;
+    for (auto &c : G.dev) c.sum_index = -1;
+    return PTB_SUCCESS;
+}
+int ptb_get_gpus(void) { return G.n_gpus; }
 
 int ptb_render(int spp) {
     NEED_INIT();
@@ -911,12 +1154,11 @@ int ptb_render(int spp) {
     bool ok = true;
     RefCamera cam = arg_val<RefCamera>(PTB_KERNEL_TRACE_RAY, 11, &ok);
     if (!ok) return fail(PTB_ERR_INVALID_ARGS, "ptb_render: trace_ray argument 11 (Camera) is not set");
+    if (G.n_gpus > 1) return render_multi((size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
     RenderParams p;
     rc = make_params(p, (size_t)(int)cam.XM, (size_t)(int)cam.YM, spp, false);
     if (rc) return rc;
-    if (want_pool(p)) return run_pool(p);
-    if (G.pipe != PTB_PIPE_MEGAKERNEL && p.accel == PT_ACCEL_LBVH) return run_wavefront(p);   // tiny scenes: the megakernel's shared-memory scan
-    return run_render(p);
+    return run_any(p, true);                 // LBVH scenes: pool kernel or wavefront; tiny scenes: the megakernel's shared-memory scan
 }
 
 int ptb_closest_hit(ptb_mem rays_h, size_t n_rays, ptb_mem out_h) {
@@ -937,10 +1179,10 @@ int ptb_closest_hit(ptb_mem rays_h, size_t n_rays, ptb_mem out_h) {
     if (want_pool(p)) {
         rc = ensure_pool_blob();
         if (rc) return rc;
-        const int kp = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, G.pool_blob, G.stream)
-                                                 : pt_fast::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, G.pool_blob, G.stream);
+        const int kp = G.math == PTB_MATH_PARITY ? pt_parity::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, D().pool_blob, S())
+                                                 : pt_fast::launch_pool_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, D().pool_blob, S());
         cudaError_t ep = cudaGetLastError();
-        if (ep == cudaSuccess) ep = cudaStreamSynchronize(G.stream);
+        if (ep == cudaSuccess) ep = cudaStreamSynchronize(S());
         if (ep != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_closest_hit: %s", cudaGetErrorString(ep));
         G.launches += (unsigned long long)kp;
         out->version++;
@@ -950,10 +1192,10 @@ int ptb_closest_hit(ptb_mem rays_h, size_t n_rays, ptb_mem out_h) {
     void *scratch = nullptr;
     if (wf) CUDA_OK(cudaMalloc(&scratch, n_rays * 36 + 64));
     const int k = G.math == PTB_MATH_PARITY
-                      ? pt_parity::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, G.stream)
-                      : pt_fast::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, G.stream);
+                      ? pt_parity::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, S())
+                      : pt_fast::launch_closest_hit(p, (const RefRay *)rays->dptr, n_rays, (float2 *)out->dptr, wf, scratch, S());
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(G.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(S());
     cudaFree(scratch);
     if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_closest_hit: %s", cudaGetErrorString(e));
     G.launches += (unsigned long long)k;
@@ -981,7 +1223,7 @@ int ptb_resolve_sum(ptb_mem colors_sum, int total_spp) {
     if (n > 0x7fffffffu) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_sum: buffer too large");
     ResolveSrc src{};
     src.p[0] = (const float4 *)m->dptr; src.n = 1;
-    resolve_frame(src, 1.0f / (float)total_spp, (int)n, 1, 0, (float4 *)m->dptr, nullptr, nullptr, G.stream);
+    resolve_frame(src, 1.0f / (float)total_spp, (int)n, 1, 0, (float4 *)m->dptr, nullptr, nullptr, S());
     CUDA_OK(cudaGetLastError());
     G.launches++;
     m->version++;
@@ -997,17 +1239,25 @@ int ptb_get_counters(ptb_counters *out) {
     if (!out) return PTB_ERR_INVALID_VALUE;
     int rc = flush_pending();
     if (rc) return rc;
-    unsigned long long h[PT_CNT_WORDS];
-    CUDA_OK(cudaMemcpyAsync(h, G.counters, sizeof h, cudaMemcpyDeviceToHost, G.stream));
-    CUDA_OK(cudaStreamSynchronize(G.stream));
-    out->rays = h[PT_CNT_RAYS]; out->box_tests = h[PT_CNT_BOX]; out->tri_tests = h[PT_CNT_TRI];
-    out->tri_stage1 = h[PT_CNT_TRI1]; out->tri_stage2 = h[PT_CNT_TRI2]; out->tri_stage3 = h[PT_CNT_TRI3];
-    out->pixel_samples = h[PT_CNT_PIXEL_SAMPLES];
+    unsigned long long tot[PT_CNT_WORDS] = {0};
+    for (int d = 0; d < G.n_gpus; ++d) {
+        DevScope scope(d);
+        unsigned long long h[PT_CNT_WORDS];
+        CUDA_OK(cudaMemcpyAsync(h, D().counters, sizeof h, cudaMemcpyDeviceToHost, S()));
+        CUDA_OK(cudaStreamSynchronize(S()));
+        for (int k = 0; k < PT_CNT_WORDS; ++k) tot[k] += h[k];
+    }
+    out->rays = tot[PT_CNT_RAYS]; out->box_tests = tot[PT_CNT_BOX]; out->tri_tests = tot[PT_CNT_TRI];
+    out->tri_stage1 = tot[PT_CNT_TRI1]; out->tri_stage2 = tot[PT_CNT_TRI2]; out->tri_stage3 = tot[PT_CNT_TRI3];
+    out->pixel_samples = tot[PT_CNT_PIXEL_SAMPLES];
     return PTB_SUCCESS;
 }
 int ptb_reset_counters(void) {
     NEED_INIT();
-    CUDA_OK(cudaMemsetAsync(G.counters, 0, PT_CNT_WORDS * sizeof(unsigned long long), G.stream));
+    for (int d = 0; d < G.n_gpus; ++d) {
+        DevScope scope(d);
+        CUDA_OK(cudaMemsetAsync(D().counters, 0, PT_CNT_WORDS * sizeof(unsigned long long), S()));
+    }
     return PTB_SUCCESS;
 }
 
@@ -1029,13 +1279,13 @@ int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int 
     ResolveSrc src{};
     src.p[0] = (const float4 *)m->dptr; src.n = 1;
     resolve_frame(src, divide_by > 1 ? 1.0f / (float)divide_by : 1.0f, width, height, mode, divide_by > 1 ? (float4 *)m->dptr : nullptr,
-                  im ? (float4 *)im->dptr : nullptr, d, G.stream);
+                  im ? (float4 *)im->dptr : nullptr, d, S());
     cudaError_t e = cudaGetLastError();
     G.launches++;
     if (divide_by > 1) m->version++;
     if (im) im->version++;
-    if (e == cudaSuccess && dst_host) e = cudaMemcpyAsync(dst_host, d, n * 4, cudaMemcpyDeviceToHost, G.stream);
-    if (e == cudaSuccess && dst_host) e = cudaStreamSynchronize(G.stream);
+    if (e == cudaSuccess && dst_host) e = cudaMemcpyAsync(dst_host, d, n * 4, cudaMemcpyDeviceToHost, S());
+    if (e == cudaSuccess && dst_host) e = cudaStreamSynchronize(S());
     cudaFree(d);
     if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_resolve_frame: %s", cudaGetErrorString(e));
     return PTB_SUCCESS;
@@ -1048,7 +1298,7 @@ int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height) {
         return fail(PTB_ERR_INVALID_VALUE, "ptb_filter_median: bad arguments");
     int rc = flush_pending();
     if (rc) return rc;
-    filter_median((const float4 *)c->dptr, (float4 *)im->dptr, width, height, G.stream);
+    filter_median((const float4 *)c->dptr, (float4 *)im->dptr, width, height, S());
     CUDA_OK(cudaGetLastError());
     G.launches++;
     im->version++;
@@ -1080,7 +1330,7 @@ int ptb_comm_reduce(ptb_mem colors, int root) {
     if (rc) return rc;
     if (comm_ranks() == 1) return PTB_SUCCESS;
     char err[256];
-    if (comm_reduce_sum((float *)m->dptr, m->bytes / sizeof(float), root, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    if (comm_reduce_sum((float *)m->dptr, m->bytes / sizeof(float), root, S(), err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
     m->version++;
     return PTB_SUCCESS;
 }
@@ -1092,7 +1342,7 @@ int ptb_comm_broadcast(ptb_mem buf, int root) {
     if (rc) return rc;
     if (comm_ranks() == 1) return PTB_SUCCESS;
     char err[256];
-    if (comm_broadcast(m->dptr, m->bytes, root, G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    if (comm_broadcast(m->dptr, m->bytes, root, S(), err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
     m->version++;
     return PTB_SUCCESS;
 }
@@ -1101,7 +1351,7 @@ int ptb_comm_barrier(void) {
     int rc = flush_pending();
     if (rc) return rc;
     char err[256];
-    if (comm_barrier(G.stream, err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    if (comm_barrier(S(), err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
     return PTB_SUCCESS;
 }
 int ptb_comm_destroy(void) { return comm_destroy(); }
@@ -1165,14 +1415,14 @@ int ptb_set_stream(void *cuda_stream) {
     NEED_INIT();
     int rc = flush_pending();
     if (rc) return rc;
-    CUDA_OK(cudaStreamSynchronize(G.stream));
+    CUDA_OK(cudaStreamSynchronize(S()));
     G.stream = cuda_stream ? (cudaStream_t)cuda_stream : G.own_stream;
     return PTB_SUCCESS;
 }
 void *ptb_get_stream(void) { return (void *)G.stream; }
 int ptb_accel_stats(int *n_nodes, int *n_tris, int *max_depth, float *build_ms) {
-    const Lbvh &b = G.staged.lbvh;
-    bool v = G.staged.lbvh_valid;
+    const Lbvh &b = D().staged.lbvh;
+    bool v = D().staged.lbvh_valid;
     if (n_nodes) *n_nodes = v ? b.n_nodes : 0;
     if (n_tris) *n_tris = v ? b.n_tris : 0;
     if (max_depth) *max_depth = v ? b.max_depth : 0;

@@ -385,6 +385,7 @@ int ptb_filter_median(ptb_mem colors, ptb_mem image, int w, int h) {
     ptb_set_arg_mem(PTB_KERNEL_FILT_IM, 1, colors);
     return ptb_launch(PTB_KERNEL_FILT_IM, (size_t)w, (size_t)h);
 }
+int ptb_set_gpus(int n, int) { return n == 1 ? PTB_SUCCESS : fail(PTB_ERR_INVALID_VALUE, "the CPU oracle is one device"); }
 int ptb_set_stream(void *) { return PTB_SUCCESS; }
 void *ptb_get_stream(void) { return nullptr; }
 int ptb_accel_stats(int *a, int *b, int *c, float *d) {

@@ -102,6 +102,7 @@ int main(int argc, char **argv) {
     int W = 0, H = 0, spp = 1, iters = 4, threads = 0, accel = -1, math = -1;
     bool brute = false, count = false, no_bvh = false, use_render_ext = false;
     int shard[3] = {0, 1, 1};
+    int gpus = 1, gpu_split = PTB_SPLIT_TILE, pipeline = -1;
     float fov = 39.3f, cyaw = 0.0f, cpitch = 0.0f, eye[3] = {277.5f, 277.5f, -800.0f};
     std::vector<ObjSpec> objs;
     std::vector<std::string> tribins;
@@ -125,6 +126,9 @@ int main(int argc, char **argv) {
         else if (a == "--cam-pitch") { need(i, 1); cpitch = (float)atof(argv[++i]); }
         else if (a == "--eye") { need(i, 3); for (int k = 0; k < 3; ++k) eye[k] = (float)atof(argv[++i]); }
         else if (a == "--shard") { need(i, 3); for (int k = 0; k < 3; ++k) shard[k] = atoi(argv[++i]); }
+        else if (a == "--gpus") { need(i, 1); gpus = atoi(argv[++i]); }
+        else if (a == "--split") { need(i, 1); gpu_split = std::string(argv[++i]) == "spp" ? PTB_SPLIT_SPP : PTB_SPLIT_TILE; }
+        else if (a == "--pipeline") { need(i, 1); pipeline = atoi(argv[++i]); }
         else if (a == "--obj") { need(i, 1); ObjSpec o; o.file = argv[++i]; objs.push_back(o); }
         else if (a == "--pos") { need(i, 3); for (int k = 0; k < 3; ++k) objs.back().pos[k] = (float)atof(argv[++i]); }
         else if (a == "--scale") { need(i, 3); for (int k = 0; k < 3; ++k) objs.back().scale[k] = (float)atof(argv[++i]); }
@@ -176,6 +180,9 @@ int main(int argc, char **argv) {
     if (math >= 0) ptb_set_math(math);
     if (count) ptb_set_count_work(1);
     if (shard[1] > 1) ptb_set_pixel_shard(shard[0], shard[1], shard[2]);
+    if (pipeline >= 0) ptb_set_pipeline(pipeline);
+    // the ONE call a multi-GPU host adds: the launches of Scene::render (main.cpp:683-687) then run on `gpus` GPUs
+    if (gpus > 1) ptb_set_gpus(gpus, gpu_split);
     ptb_build_accel();
     ptb_reset_counters();
 
