@@ -94,6 +94,9 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
 #define PI(f, s) wi[(f) * POOL_NS + (s)]
     const int n_big_pairs = MODE == 0 ? wf_stage_big(p, s_big) : 0;
     Work wk = {0, 0, 0, 0, 0, 0, 0};
+#ifdef POOL_DEBUG_STATES   // throw-away instrumentation (scripts/pool_states.py): warp steps and served slots per phase, through the work counters
+    unsigned dbg_steps[3] = {0, 0, 0}, dbg_lanes[3] = {0, 0, 0};
+#endif
     bool exhausted = a.n_items <= 0;                  // warp-uniform: the cursor has handed out every item
     const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
     const int s_end = p.sample0 + p.spp;
@@ -121,6 +124,9 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
         const int cnt = min(c0 + __popc(m1), 32);
         const bool active = lane < cnt;
         const int slot = active ? sel[lane] : 0;
+#ifdef POOL_DEBUG_STATES
+        dbg_steps[phase] += 1; dbg_lanes[phase] += cnt;
+#endif
         if (phase == 0) {
             // -------------------------------------------------------- NODE: pop (if the slot needs one), then the wide node's four slab tests
             int tg = PL_DEAD, link = 0, sp = 0;
@@ -299,6 +305,10 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
     }
 #undef PF
 #undef PI
+#ifdef POOL_DEBUG_STATES
+    if (COUNT) { const bool l0_ = lane == 0; wk.box = l0_ ? dbg_steps[0] : 0; wk.tri = l0_ ? dbg_lanes[0] : 0; wk.tri1 = l0_ ? dbg_steps[1] : 0;
+                 wk.tri2 = l0_ ? dbg_lanes[1] : 0; wk.tri3 = l0_ ? dbg_steps[2] : 0; wk.samples = l0_ ? dbg_lanes[2] : 0; }
+#endif
     wf_flush_counters(p, wk, COUNT);
 }
 

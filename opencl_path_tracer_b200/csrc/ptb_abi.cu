@@ -143,7 +143,7 @@ struct State {
 // during static destruction, after which ptb_release still gets called
 State &G = *new State();
 inline DevCtx &D() { return G.dev[G.cur]; }                                    // the device the launch path is working on
-inline cudaStream_t S() { return G.cur == 0 ? S() : G.dev[G.cur].stream; }
+inline cudaStream_t S() { return G.cur == 0 ? G.stream : G.dev[G.cur].stream; }
 
 int fail(int code, const char *fmt, ...) {
     char buf[512];
@@ -532,7 +532,8 @@ int run_wavefront(RenderParams &p) {
 
 // persistent pool kernel (pt_pool.cuh): does this launch go through it?
 bool want_pool(const RenderParams &p) {
-    if (p.from_rays || p.accel != PT_ACCEL_LBVH) return false;
+    static const bool disabled = getenv("PTB_DISABLE_POOL") && atoi(getenv("PTB_DISABLE_POOL"));     // experiments / bisecting only
+    if (disabled || p.from_rays || p.accel != PT_ACCEL_LBVH) return false;
     if (!(G.pipe == PTB_PIPE_POOL || (G.pipe == PTB_PIPE_AUTO && G.auto_pool))) return false;
     return G.math == PTB_MATH_PARITY ? pt_parity::pool_usable(p) : pt_fast::pool_usable(p);
 }

@@ -71,7 +71,7 @@ ALL_ACCELS = [capi.ACCEL_BRUTE, capi.ACCEL_REFBVH, capi.ACCEL_LBVH]
 
 
 @pytest.mark.parametrize("accel", ALL_ACCELS)
-@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT])
+@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
 def test_empty_scene_is_black_and_still_draws_the_camera_jitter(ptb, accel, pipeline):
     got, rnds, want, wrnds = both(ptb, build([], 37, 19, 4), 3, accel, pipeline)
     assert (got[..., :3] == 0).all() and same_bits(got, want)
@@ -87,11 +87,11 @@ def test_tiny_scenes_single_leaf_and_single_node_trees(ptb, accel, n_tris):
 
 
 @pytest.mark.parametrize("size", [(1, 1), (7, 3), (33, 17), (130, 9), (17, 129)])
-@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT])
+@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
 def test_ragged_launch_sizes(ptb, size, pipeline):
     """widths/heights that are no multiple of the 16x8 block or the 8x4 warp tile, down to one pixel"""
     W, H = size
-    accel = capi.ACCEL_LBVH if pipeline == capi.PIPE_WAVEFRONT else capi.ACCEL_BRUTE
+    accel = capi.ACCEL_LBVH if pipeline != capi.PIPE_MEGAKERNEL else capi.ACCEL_BRUTE
     got, rnds, want, wrnds = both(ptb, build(open_box(), W, H, 4), 5, accel, pipeline)
     assert same_bits(got, want) and (rnds == wrnds).all()
     assert got[..., :3].sum() > 0 or W * H < 16
@@ -120,16 +120,17 @@ def test_degenerate_triangles_do_not_poison_the_image(ptb, accel):
     assert np.isfinite(got[..., :3]).all()
 
 
+@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
 @pytest.mark.parametrize("depth", [0, 1, 2, 7])
-def test_bounce_count_extremes(ptb, depth):
+def test_bounce_count_extremes(ptb, depth, pipeline):
     """iterations = 0: the bounce loop never runs (black, only the jitter draws); 1: flat preview (prog.cl:323-325)"""
-    got, rnds, want, wrnds = both(ptb, build(open_box(), 40, 30, depth), 3, capi.ACCEL_LBVH)
+    got, rnds, want, wrnds = both(ptb, build(open_box(), 40, 30, depth), 3, capi.ACCEL_LBVH, pipeline)
     assert same_bits(got, want) and (rnds == wrnds).all()
     if depth == 0:
         assert (got[..., :3] == 0).all()
 
 
-@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT])
+@pytest.mark.parametrize("pipeline", [capi.PIPE_MEGAKERNEL, capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
 def test_mirror_and_glass_inside_the_box(ptb, pipeline):
     extra = quad((-80, 0, 40), (-20, 0, 40), (-20, 90, 60), (-80, 90, 60), 3) + quad((20, 10, -20), (80, 10, -20), (80, 80, 0), (20, 80, 0), 4) \
         + quad((20, 10, 30), (80, 10, 30), (80, 80, 50), (20, 80, 50), 4)

@@ -76,8 +76,14 @@ def _worker(rank, world, port, out_dir):
     s1 = _scene(ptb)
     shared = multigpu.share_root_colors(ptb, W, H)
     s1.buffer_colors = shared
-    refreshes = []                                # progressive: 3 launches of 6/6/4 samples, the running mean is read back through the mapping
-    multigpu.render_progressive(s1, ptb, SPP, 6, on_refresh=refreshes.append)
+    refreshes, frames = [], []                    # progressive: 3 launches of 6/6/4 samples, the running mean is read back through the mapping
+
+    def on_refresh(done):                         # the root reads the WHOLE shared frame at every refresh: it must hold `done` samples of every pixel
+        refreshes.append(done)
+        if rank == 0:
+            frames.append(ptb.read(shared, np.float32, W * H * 4).reshape(H, W, 4).copy())
+
+    multigpu.render_progressive(s1, ptb, SPP, 6, on_refresh=on_refresh)
     assert refreshes == [6, 12, 16]
     peer = ptb.read(shared, np.float32, W * H * 4).reshape(H, W, 4) if rank == 0 else np.zeros((H, W, 4), np.float32)
     dist.barrier()
@@ -109,7 +115,8 @@ def _worker(rank, world, port, out_dir):
         ptb.finish()
     merged = frame2.colors.cpu().numpy().reshape(H, W, 4)
     ptb.set_accumulate_sum(0)
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), tile=tile, mine=mine, merged=merged, peer=peer)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), tile=tile, mine=mine, merged=merged, peer=peer,
+             refresh=np.stack(frames) if frames else np.zeros((0, H, W, 4), np.float32))
     dist.barrier()
     ptb.comm_destroy()
     dist.destroy_process_group()
@@ -130,13 +137,19 @@ def test_two_gpus_tile_split_is_bitwise_and_spp_split_converges(ptb, tmp_path):
     # single-GPU renders in this process
     ptb.set_accel(capi.ACCEL_BRUTE); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(capi.PIPE_MEGAKERNEL)
     s = _scene(ptb)
-    s.render_spp(SPP)
-    one = s.download_colors().copy()
+    partial = []
+    for n in (6, 6, 4):                                    # the refresh points of the progressive run
+        s.render_spp(n)
+        partial.append(s.download_colors().copy())
+    one = partial[-1]
     s.render_spp(SPP)                                      # ... continued to 2*SPP samples
     two = s.download_colors().copy()
     ptb.finish()
     assert (bits(r0["tile"]) == bits(one)).all() and (bits(r1["tile"]) == bits(one)).all()
     assert (bits(r0["peer"]) == bits(one)).all()           # peer-memory gather, three progressive launches: the same bits on rank 0
+    assert len(r0["refresh"]) == 3                         # ... and every refresh frame is the 1-GPU frame at that sample count (no torn reads)
+    for got, want in zip(r0["refresh"], partial):
+        assert (bits(got) == bits(want)).all()
     # rank 0's SUM buffer / SPP is the 1-GPU mean up to the rounding of sum-vs-running-mean
     assert np.abs(r0["mine"][..., :3] / SPP - one[..., :3]).max() <= 2e-5 * max(1.0, float(one[..., :3].max()))
     # the merged image is a 2*SPP estimate from different random numbers: same expectation, Monte-Carlo distance
