@@ -24,7 +24,7 @@ SYMBOLS = [
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
     "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit", "ptb_invalidate", "ptb_resolve_frame", "ptb_save_state", "ptb_load_state",
     "ptb_comm_unique_id", "ptb_comm_init", "ptb_comm_ranks", "ptb_comm_rank", "ptb_comm_reduce", "ptb_comm_broadcast", "ptb_comm_barrier", "ptb_comm_destroy",
-    "ptb_set_gpus", "ptb_get_gpus",
+    "ptb_set_gpus", "ptb_get_gpus", "ptb_set_quant_nodes",
 ]
 
 
@@ -74,7 +74,7 @@ def load_library(path=None):
         "ptb_invalidate": (i, [u64]), "ptb_resolve_frame": (i, [u64, i, i, i, i, u64, vp]),
         "ptb_save_state": (i, [cp]), "ptb_load_state": (i, [cp, C.POINTER(i)]),
         "ptb_comm_unique_id": (i, [vp]), "ptb_comm_init": (i, [i, i, vp]), "ptb_comm_ranks": (i, []), "ptb_comm_rank": (i, []),
-        "ptb_set_gpus": (i, [i, i]), "ptb_get_gpus": (i, []),
+        "ptb_set_quant_nodes": (i, [i]), "ptb_set_gpus": (i, [i, i]), "ptb_get_gpus": (i, []),
         "ptb_comm_reduce": (i, [u64, i]), "ptb_comm_broadcast": (i, [u64, i]), "ptb_comm_barrier": (i, []), "ptb_comm_destroy": (i, []),
     }
     for name, (res, args) in proto.items():
@@ -234,6 +234,7 @@ class Ptb:
     def set_accel(self, a): self._ck(self.lib.ptb_set_accel(a), "ptb_set_accel")
     def set_math(self, m): self._ck(self.lib.ptb_set_math(m), "ptb_set_math")
     def set_pipeline(self, p): self._ck(self.lib.ptb_set_pipeline(p), "ptb_set_pipeline")
+    def set_quant_nodes(self, on): self._ck(self.lib.ptb_set_quant_nodes(int(on)), "ptb_set_quant_nodes")
     def set_wf_subs(self, n): self._ck(self.lib.ptb_set_wf_subs(n), "ptb_set_wf_subs")
     def set_fuse_gen(self, on): self._ck(self.lib.ptb_set_fuse_gen(int(on)), "ptb_set_fuse_gen")
     def set_lbvh_leaf(self, n): self._ck(self.lib.ptb_set_lbvh_leaf(n), "ptb_set_lbvh_leaf")

@@ -307,6 +307,71 @@ __global__ void k_emit4(int n, int leaf_size, float eps, const int2 *range, cons
     o[7] = make_float4(__int_as_float(ns), 0.0f, 0.0f, 0.0f);
 }
 
+// ---- quantised 4-ary nodes: 64 bytes instead of 128, so that a node is TWO 256-bit loads (two L1 wavefronts per lane) instead
+// of five fetches — the L1 data pipes, one wavefront per lane and scattered access, are what bounds the traversal
+// (profiles/r02_pool_v1.txt).  Layout, 16 words:
+//   w0-2  origin p (float): two quantisation steps below the union box of the children
+//   w3    biased exponents ex | ey << 8 | ez << 16 of 128 * step (step = 2^k per axis, >= extent / 250)
+//   w4-9  per axis the four children's lower bounds (one byte each), then their upper bounds: x lo, x hi, y lo, y hi, z lo, z hi
+//   w12-15 links (same encoding as the 128-byte node)
+// A child's box is [p + qlo * step, p + qhi * step] with qlo = floor(..) - 1 and qhi = ceil(..) + 1: it contains the (already
+// eps-inflated) float box with a whole step to spare on every side, which covers the rounding of the decode in the
+// traversal (< 2^-8 step, see k_pool).  Empty slot: qlo = 255, qhi = 0 (inverted on every axis: never hit).
+__global__ void k_emit4q(int n, int leaf_size, float eps, const int2 *range, const int2 *child, const int *flag, const int *id4,
+                         const float4 *leaf_lo, const float4 *leaf_hi, const float4 *node_lo, const float4 *node_hi, uint4 *bvh4q) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1 || !flag[i]) return;
+    Slot s[4];
+    int ns = 0;
+    const int2 c = child[i];
+    const int cc[2] = {c.x, c.y};
+    for (int k = 0; k < 2; ++k) {
+        Slot t;
+        if (slot_of(cc[k], leaf_size, range, id4, leaf_lo, leaf_hi, node_lo, node_hi, t)) { s[ns++] = t; continue; }
+        const int2 g = child[cc[k]];
+        const int gg[2] = {g.x, g.y};
+        for (int j = 0; j < 2; ++j) {
+            slot_of(gg[j], leaf_size, range, id4, leaf_lo, leaf_hi, node_lo, node_hi, t);
+            s[ns++] = t;
+        }
+    }
+    float lo[4][3], hi[4][3], ulo[3] = {3e38f, 3e38f, 3e38f}, uhi[3] = {-3e38f, -3e38f, -3e38f};
+    for (int k = 0; k < ns; ++k) {
+        lo[k][0] = s[k].lo.x - eps; lo[k][1] = s[k].lo.y - eps; lo[k][2] = s[k].lo.z - eps;
+        hi[k][0] = s[k].hi.x + eps; hi[k][1] = s[k].hi.y + eps; hi[k][2] = s[k].hi.z + eps;
+        for (int a = 0; a < 3; ++a) { ulo[a] = fminf(ulo[a], lo[k][a]); uhi[a] = fmaxf(uhi[a], hi[k][a]); }
+    }
+    unsigned w[16];
+    for (int k = 0; k < 16; ++k) w[k] = 0u;
+    unsigned exps = 0u;
+    for (int a = 0; a < 3; ++a) {
+        float ext = uhi[a] - ulo[a];
+        if (!(ext > 1e-30f)) ext = 1e-30f;
+        int e2 = 0;
+        frexpf(ext * (1.0f / 250.0f), &e2);                 // ext / 250 = m * 2^e2, m in [0.5, 1): step = 2^e2 >= ext / 250
+        e2 = max(-120, min(120, e2));
+        const float step = ldexpf(1.0f, e2), inv_step = ldexpf(1.0f, -e2);
+        const float p = ulo[a] - 2.0f * step;
+        w[a] = __float_as_uint(p);
+        exps |= (unsigned)(e2 + 7 + 127) << (8 * a);
+        unsigned qlo = 0u, qhi = 0u;
+        for (int k = 0; k < 4; ++k) {
+            int ql = 255, qh = 0;
+            if (k < ns) {
+                ql = (int)floorf((lo[k][a] - p) * inv_step) - 1;
+                qh = (int)ceilf((hi[k][a] - p) * inv_step) + 1;
+                ql = max(0, min(255, ql)); qh = max(0, min(255, qh));
+            }
+            qlo |= (unsigned)ql << (8 * k); qhi |= (unsigned)qh << (8 * k);
+        }
+        w[4 + 2 * a] = qlo; w[5 + 2 * a] = qhi;
+    }
+    w[3] = exps;
+    for (int k = 0; k < 4; ++k) w[12 + k] = (unsigned)(k < ns ? s[k].link : leaf_link(0, 1));
+    uint4 *o = bvh4q + 4 * (size_t)id4[i];
+    for (int r = 0; r < 4; ++r) o[r] = make_uint4(w[4 * r], w[4 * r + 1], w[4 * r + 2], w[4 * r + 3]);
+}
+
 // depth of every triangle's leaf in the EMITTED tree = number of emitted ancestors
 __global__ void k_depth(int n, int leaf_size, const int2 *range, const int *parent_of_node, const int *parent_of_leaf, int *max_depth, int *n_emitted) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
@@ -330,13 +395,13 @@ __global__ void k_depth(int n, int leaf_size, const int2 *range, const int *pare
 
 }  // namespace
 
-static cudaTextureObject_t linear_tex(const float4 *p, size_t count) {
+static cudaTextureObject_t linear_tex(const float4 *p, size_t count, bool as_uint = false) {
     if (!p || count == 0) return 0;
     cudaResourceDesc rd;
     memset(&rd, 0, sizeof rd);
     rd.resType = cudaResourceTypeLinear;
     rd.res.linear.devPtr = const_cast<float4 *>(p);
-    rd.res.linear.desc = cudaCreateChannelDesc<float4>();
+    rd.res.linear.desc = as_uint ? cudaCreateChannelDesc<uint4>() : cudaCreateChannelDesc<float4>();     // quantised nodes are bit patterns, not floats
     rd.res.linear.sizeInBytes = count * sizeof(float4);
     cudaTextureDesc td;
     memset(&td, 0, sizeof td);
@@ -350,6 +415,7 @@ void lbvh_free(Lbvh *b) {
     if (!b) return;
     if (b->bvh_tex) cudaDestroyTextureObject(b->bvh_tex);
     if (b->bvh4_tex) cudaDestroyTextureObject(b->bvh4_tex);
+    if (b->bvh4q_tex) cudaDestroyTextureObject(b->bvh4q_tex);
     cudaFree(b->arena);
     memset(b, 0, sizeof(*b));
 }
@@ -373,7 +439,7 @@ struct Scratch {
 // the layout is a function of the capacity alone, so the pointers stay put across rebuilds
 size_t lbvh_carve(Lbvh *b, Scratch &t, char *base, size_t cap, size_t sort_bytes, size_t scan_bytes) {
     Carver c{base, 0};
-    b->bvh = c.take<float4>(4 * cap); b->bvh4 = c.take<float4>(8 * cap);
+    b->bvh = c.take<float4>(4 * cap); b->bvh4 = c.take<float4>(8 * cap); b->bvh4q = c.take<float4>(4 * cap);
     b->parent = c.take<int>(cap); b->flag4 = c.take<int>(cap); b->id4 = c.take<int>(cap + 1);
     b->sq0 = c.take<float4>(cap); b->sq1 = c.take<float4>(cap); b->sq2 = c.take<float4>(cap);
     b->sf0 = c.take<float4>(cap); b->sf1 = c.take<float4>(cap); b->sf2 = c.take<float4>(cap);
@@ -406,6 +472,10 @@ int lbvh_emit(Lbvh *b, float reach, cudaStream_t st, char *err, size_t errcap) {
                                                         b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, b->bvh4);
             CK(cudaGetLastError());
             b->launches++;
+            k_emit4q<<<(n - 1 + 255) / 256, 256, 0, st>>>(n, b->leaf_size, eps, (const int2 *)b->range, (const int2 *)b->child, b->flag4, b->id4,
+                                                         b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, (uint4 *)b->bvh4q);
+            CK(cudaGetLastError());
+            b->launches++;
         }
     }
     return 0;
@@ -415,6 +485,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
                int n, int leaf_size, float big_frac, cudaStream_t st, char *err, size_t errcap) {
     if (b->bvh_tex) cudaDestroyTextureObject(b->bvh_tex);
     if (b->bvh4_tex) cudaDestroyTextureObject(b->bvh4_tex);
+    if (b->bvh4q_tex) cudaDestroyTextureObject(b->bvh4q_tex);
     {   // forget the previous tree, keep the arena
         void *arena = b->arena; const size_t arena_bytes = b->arena_bytes; const int cap = b->cap;
         memset(b, 0, sizeof(*b));
@@ -499,6 +570,7 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     if (lbvh_emit(b, 0.0f, st, err, errcap)) return -1;
     if (m >= 2 && (size_t)4 * m < ((size_t)1 << 27)) b->bvh_tex = linear_tex(b->bvh, (size_t)4 * m);
     if (b->n_nodes4 > 0 && (size_t)8 * b->n_nodes4 < ((size_t)1 << 27)) b->bvh4_tex = linear_tex(b->bvh4, (size_t)8 * b->n_nodes4);
+    if (b->n_nodes4 > 0 && (size_t)4 * b->n_nodes4 < ((size_t)1 << 27)) b->bvh4q_tex = linear_tex(b->bvh4q, (size_t)4 * b->n_nodes4, true);
     CK(cudaEventRecord(e1, st));
     CK(cudaEventSynchronize(e1));
     CK(cudaEventElapsedTime(&b->build_ms, e0, e1));

@@ -11,8 +11,10 @@ struct Lbvh {
     // traversal data
     float4 *bvh;                  // 4 float4 per node
     float4 *bvh4;                 // 8 float4 per 4-ary node (root = node 0), n_nodes4 of them; null when the root is a leaf
+    float4 *bvh4q;                // the same wide nodes quantised to 64 bytes (8-bit child boxes against the node's own origin / step), lbvh.cu
     int n_nodes4;
     cudaTextureObject_t bvh_tex, bvh4_tex;   // the node arrays as linear float4 textures (fetches go through the TEX data pipe)
+    cudaTextureObject_t bvh4q_tex;           // bvh4q as a linear uint4 texture
     int *parent, *flag4, *id4;    // binary parent links; which binary nodes are wide nodes; their compact ids
     float4 *sq0, *sq1, *sq2;      // triangles in Morton order, parity layout (vertices + normal)
     float4 *sf0, *sf1, *sf2;      // triangles in Morton order, fast layout (normal, anchor, barycentric gradients)

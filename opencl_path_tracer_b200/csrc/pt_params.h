@@ -33,6 +33,8 @@ struct SceneDev {
     // GPU-built LBVH (lbvh.cu)
     const float4 *bvh;            // 4 float4 per node: both children's boxes + links (lbvh.cu)
     cudaTextureObject_t bvh_tex, bvh4_tex;   // bvh / bvh4 as linear float4 textures, 0 = fetch through the LSU
+    cudaTextureObject_t bvh4q_tex;           // bvh4q as a linear uint4 texture, 0 = fetch through the LSU
+    const float4 *bvh4q;          // the 4-ary nodes quantised to 64 bytes (lbvh.cu k_emit4q); null: traverse the float nodes
     const float4 *bvh4;           // the same tree collapsed to 4-ary nodes, 8 float4 each (lbvh.cu); null: not usable
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order

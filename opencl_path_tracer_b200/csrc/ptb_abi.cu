@@ -137,6 +137,7 @@ struct State {
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
     unsigned long long launches = 0;
     PendingGen pending;
+    int quant_nodes = 1;               // pool kernel: traverse the 64-byte quantised wide nodes (PTB_QUANT_NODES=0: the 128-byte float nodes)
     int auto_pool = 0;                 // PTB_PIPE_AUTO on LBVH scenes: 1 = the pool kernel, 0 = the wavefront (PTB_AUTO_POOL)
 };
 // immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
@@ -412,6 +413,8 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         // the 4-ary traversal pushes up to 3 entries per level: usable when the stack bound (64) covers the tree
         const int wide_levels = (s.lbvh.max_depth + 1) / 2;
         p.sc.bvh4 = (G.wide_bvh && s.lbvh.n_nodes4 > 0 && 3 * wide_levels + 1 <= 64) ? s.lbvh.bvh4 : nullptr;
+        p.sc.bvh4q = (p.sc.bvh4 && G.quant_nodes) ? s.lbvh.bvh4q : nullptr;
+        p.sc.bvh4q_tex = G.tex_nodes ? s.lbvh.bvh4q_tex : 0;
         p.sc.n_nodes4 = s.lbvh.n_nodes4;
         p.sc.srec = fastm ? s.lbvh.rf : s.lbvh.rq;
         p.sc.sq0 = fastm ? s.lbvh.sf0 : s.lbvh.sq0; p.sc.sq1 = fastm ? s.lbvh.sf1 : s.lbvh.sq1; p.sc.sq2 = fastm ? s.lbvh.sf2 : s.lbvh.sq2;
@@ -729,6 +732,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
     if ((env = getenv("PTB_AUTO_POOL"))) G.auto_pool = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_QUANT_NODES"))) G.quant_nodes = atoi(env) ? 1 : 0;
     return PTB_SUCCESS;
 }
 
@@ -1049,6 +1053,10 @@ int ptb_set_math(int math) {
 int ptb_set_pipeline(int pipe) {
     if (pipe != PTB_PIPE_MEGAKERNEL && pipe != PTB_PIPE_WAVEFRONT && pipe != PTB_PIPE_AUTO && pipe != PTB_PIPE_POOL) return PTB_ERR_INVALID_VALUE;
     G.pipe = pipe;
+    return PTB_SUCCESS;
+}
+int ptb_set_quant_nodes(int on) {
+    G.quant_nodes = on ? 1 : 0;
     return PTB_SUCCESS;
 }
 int ptb_set_wf_subs(int n) {

@@ -41,6 +41,34 @@ def pixel_owner(width, height, nranks, group):
     return ((ids // group) % nranks).astype(np.int32)
 
 
+def owned_count(n_pixels, rank, nranks, group):
+    """how many pixel ids rank owns under ptb_set_pixel_shard(rank, nranks, group) — what the persistent pool kernel's pixel
+    cursor runs to (launch_pool, csrc/pt_pool.cuh): whole bands of `group` ids dealt round-robin, the image's last band may be short"""
+    if nranks <= 1:
+        return n_pixels
+    bands = (n_pixels + group - 1) // group
+    return sum(group if (b + 1) * group <= n_pixels else n_pixels - b * group for b in range(rank, bands, nranks))
+
+
+def owned_pixel(k, rank, nranks, group):
+    """pixel id of the k-th pixel rank owns (pool_item_pixel, csrc/pt_pool.cuh)"""
+    if nranks <= 1:
+        return k
+    band, off = divmod(k, group)
+    return (band * nranks + rank) * group + off
+
+
+def spp_split_device(sample_index, nranks):
+    """single-process spp split (ptb_set_gpus(n, PTB_SPLIT_SPP)): the GPU that renders the sample with this running index"""
+    return sample_index % nranks
+
+
+def spp_split_count(sample0, spp, nranks, d):
+    """... and how many of the `spp` samples starting at index sample0 GPU d renders (render_multi, csrc/ptb_abi.cu)"""
+    first = (d - sample0) % nranks
+    return (spp - first + nranks - 1) // nranks if first < spp else 0
+
+
 def reduce_sum_to_root(buf, group=None):
     """The one collective of the spp-split: SUM of the per-rank accumulation buffers at rank 0."""
     if dist.is_initialized() and dist.get_world_size(group) > 1:

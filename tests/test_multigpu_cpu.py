@@ -94,3 +94,37 @@ def test_progressive_cadence_and_single_rank_sharing():
     assert scene.launches == [8, 8, 4] and seen == [8, 16, 20] and ptb.finishes == 3
     assert multigpu.share_root_colors(ptb, 16, 9) == 42 and ptb.allocs == [16 * 9 * 16]
     assert multigpu.render_progressive(scene, ptb, 0, 8) == 0 and scene.launches == [8, 8, 4]
+
+
+def test_pool_cursor_mapping_matches_the_pixel_owner():
+    """the persistent pool kernel hands out "the k-th pixel this rank owns": count and mapping must enumerate exactly the
+    rank's pixels of pixel_owner(), in increasing id order, also when the last band of the image is short"""
+    for (w, h, n, rows) in ((64, 40, 2, 8), (37, 19, 3, 8), (130, 9, 4, 8), (17, 129, 8, 8), (5, 3, 2, 8)):
+        group = multigpu.shard_group(w, rows)
+        own = multigpu.pixel_owner(w, h, n, group)
+        total = 0
+        for r in range(n):
+            cnt = multigpu.owned_count(w * h, r, n, group)
+            ids = [multigpu.owned_pixel(k, r, n, group) for k in range(cnt)]
+            assert ids == np.nonzero(own == r)[0].tolist()
+            total += cnt
+        assert total == w * h
+
+
+def test_spp_split_schedules():
+    # one process per GPU: a FIXED job of spp samples cut n ways
+    for spp in (1, 7, 64, 1024):
+        for n in (1, 2, 3, 8):
+            assert sum(multigpu.split_spp(spp, n, r) for r in range(n)) == spp
+            assert max(multigpu.split_spp(spp, n, r) for r in range(n)) - min(multigpu.split_spp(spp, n, r) for r in range(n)) <= 1
+    # single process (ptb_set_gpus): sample with running index i goes to GPU i % n, across calls of any size
+    for n in (2, 3, 8):
+        done = 0
+        per_dev = [0] * n
+        for spp in (1, 1, 5, 16, 3):
+            counts = [multigpu.spp_split_count(done, spp, n, d) for d in range(n)]
+            want = [sum(1 for j in range(spp) if multigpu.spp_split_device(done + j, n) == d) for d in range(n)]
+            assert counts == want and sum(counts) == spp
+            per_dev = [a + b for a, b in zip(per_dev, counts)]
+            done += spp
+        assert max(per_dev) - min(per_dev) <= 1
