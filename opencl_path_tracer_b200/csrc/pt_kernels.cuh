@@ -721,7 +721,12 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
     Path ps;
     path_reset(ps);
     for (;;) {
-        if (!alive && s < s_end) {                               // path regeneration: next sample of this pixel
+        // path regeneration: the next sample of this pixel starts when at least p.regen_min lanes of the warp are waiting for one (or
+        // nobody has a path left) — the camera code then runs at that many lanes instead of at however many paths just ended (9 of 32
+        // on Cornell, profiles/r01_render_v7.txt); a waiting lane rides through the scan predicated off meanwhile
+        const bool waiting = !alive && s < s_end;
+        const int n_wait = __popc(__ballot_sync(0xffffffffu, waiting));
+        if (waiting && (n_wait >= p.regen_min || !__any_sync(0xffffffffu, alive))) {
             if (p.from_rays) {                                   // drop-in trace_ray: gen_ray already ran
                 const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
                 rayP = v3(r[0]); rayD = v3(r[1]);

@@ -77,6 +77,7 @@ struct RenderParams {
     int wf_subs;                  // wavefront: interleaved sub-wavefronts on separate streams (1..4; 0 = default 2)
     int wf_sort;                  // wavefront: group each shade block's surviving rays by direction octant in the next queue
     int parity_filter;            // parity flavour, brute force: conservative FFMA2 pre-filter in front of the exact test (pt_kernels.cuh)
+    int regen_min;                // megakernel: lanes of a warp that must be waiting for their next sample before the camera code runs (1 = at once)
     int rng_nonneg;               // 1: every RNG state of this launch was verified to lie in [0, 2^31) (pt_rand_nonneg)
     unsigned long long *counters; // PT_CNT_WORDS words
     // wavefront pipeline scratch (pt_wavefront.cuh), one path per pixel, allocated by ptb_abi.cu; null = megakernel only

@@ -137,8 +137,10 @@ struct State {
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
     unsigned long long launches = 0;
     PendingGen pending;
+    int regen_min = 1;                 // k_render: batch path regeneration until this many lanes of a warp wait (PTB_REGEN_MIN)
     int quant_nodes = 1;               // pool kernel: traverse the 64-byte quantised wide nodes (PTB_QUANT_NODES=0: the 128-byte float nodes)
-    int auto_pool = 0;                 // PTB_PIPE_AUTO on LBVH scenes: 1 = the pool kernel, 0 = the wavefront (PTB_AUTO_POOL)
+    int auto_pool = 2;                 // PTB_PIPE_AUTO on LBVH scenes: 0 = the wavefront, 1 = the pool kernel, 2 = by owned pixels (PTB_AUTO_POOL)
+    long long auto_pool_pixels = 1500000;   // ... the pool kernel up to this many pixels on this GPU (PTB_AUTO_POOL_PIXELS)
 };
 // immortal: the reference keeps its Scene (and thus its cl::Buffers) in a global that is destroyed
 // during static destruction, after which ptb_release still gets called
@@ -386,6 +388,7 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
     p.sc.q0 = fastm ? s.f0 : s.q0; p.sc.q1 = fastm ? s.f1 : s.q1; p.sc.q2 = fastm ? s.f2 : s.q2; p.sc.mati = s.mati; p.sc.n_tris = tris_size;
     p.sc.fq0 = s.f0; p.sc.fq1 = s.f1; p.sc.fq2 = s.f2;
     p.parity_filter = G.parity_filter;
+    p.regen_min = G.regen_min;
     p.wf_sort = G.wf_sort;
     p.wf_subs = G.wf_subs;
     if (p.accel == PT_ACCEL_BRUTE && fastm) {
@@ -537,7 +540,14 @@ int run_wavefront(RenderParams &p) {
 bool want_pool(const RenderParams &p) {
     static const bool disabled = getenv("PTB_DISABLE_POOL") && atoi(getenv("PTB_DISABLE_POOL"));     // experiments / bisecting only
     if (disabled || p.from_rays || p.accel != PT_ACCEL_LBVH) return false;
-    if (!(G.pipe == PTB_PIPE_POOL || (G.pipe == PTB_PIPE_AUTO && G.auto_pool))) return false;
+    if (G.pipe != PTB_PIPE_POOL) {
+        if (G.pipe != PTB_PIPE_AUTO || G.auto_pool == 0) return false;
+        // AUTO by measurement (profiles/r02_pool_shards.txt): the wavefront wins on big frames (all paths of the frame in flight,
+        // coherent first bounces), the pool kernel when this GPU owns few pixels (no per-iteration tail: 1/8 of a 4K frame and below) and
+        // whenever several GPUs render from one process (no host loop to keep them concurrent)
+        const long long owned = (long long)p.W * p.H / (p.shard_n > 1 ? p.shard_n : 1);
+        if (G.auto_pool == 2 && G.n_gpus == 1 && owned > G.auto_pool_pixels) return false;
+    }
     return G.math == PTB_MATH_PARITY ? pt_parity::pool_usable(p) : pt_fast::pool_usable(p);
 }
 int ensure_pool_blob() {
@@ -731,8 +741,10 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_WIDE_BVH"))) G.wide_bvh = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_TEX_NODES"))) G.tex_nodes = atoi(env) ? 1 : 0;
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
-    if ((env = getenv("PTB_AUTO_POOL"))) G.auto_pool = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_AUTO_POOL"))) G.auto_pool = atoi(env) < 0 ? 0 : (atoi(env) > 2 ? 2 : atoi(env));
+    if ((env = getenv("PTB_AUTO_POOL_PIXELS"))) G.auto_pool_pixels = atoll(env);
     if ((env = getenv("PTB_QUANT_NODES"))) G.quant_nodes = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_REGEN_MIN"))) G.regen_min = atoi(env) < 1 ? 1 : (atoi(env) > 32 ? 32 : atoi(env));
     return PTB_SUCCESS;
 }
 

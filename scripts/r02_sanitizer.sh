@@ -1,12 +1,19 @@
 #!/bin/bash
-# compute-sanitizer over the small-size GPU tests: memcheck on everything small, racecheck + synccheck on the
-# kernels that communicate through shared memory / ballots (pool kernel, wavefront queues, LBVH build); summaries -> profiles/
+# compute-sanitizer over the small-size GPU tests.  ONE tool per gpurun call (B200_PROFILING.md): $1 = memcheck | racecheck | synccheck
+# memcheck: every small test incl. the pool kernel, the wavefront queues, the LBVH build, filt_im, the resolve; racecheck / synccheck: the kernels
+# that communicate through shared memory and warp votes (pool kernel, wavefront push, LBVH refit).  Summaries -> profiles/r02_sanitizer_<tool>.txt
 cd "$(dirname "$0")/.." || exit 1
+export PYTHONUNBUFFERED=1
+TOOL=${1:-memcheck}
 O=gpurun_out/sanitizer; mkdir -p $O
-T="tests/test_gpu_edges.py"
-timeout 1200 compute-sanitizer --tool memcheck --error-exitcode 9 --log-file $O/memcheck_edges.log python -m pytest $T -q -m gpu -x -p no:cacheprovider > $O/memcheck_edges.pytest 2>&1; echo "memcheck edges rc=$?"
-timeout 900 compute-sanitizer --tool racecheck --racecheck-report all --error-exitcode 9 --log-file $O/racecheck_edges.log python -m pytest $T -q -m gpu -x -p no:cacheprovider -k "ragged or mirror or bounce" > $O/racecheck_edges.pytest 2>&1; echo "racecheck edges rc=$?"
-timeout 900 compute-sanitizer --tool synccheck --error-exitcode 9 --log-file $O/synccheck_edges.log python -m pytest $T -q -m gpu -x -p no:cacheprovider -k "ragged or mirror" > $O/synccheck_edges.pytest 2>&1; echo "synccheck edges rc=$?"
-timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 --log-file $O/memcheck_out.log python -m pytest tests/test_gpu_output.py -q -m gpu -x -p no:cacheprovider -k "filt_im and not 1920 or texture or resolve or checkpoint" > $O/memcheck_out.pytest 2>&1; echo "memcheck output rc=$?"
-for f in $O/*.log; do echo "== $f"; grep -E "ERROR SUMMARY|RACECHECK SUMMARY|hazard|Invalid|error" $f | sort | uniq -c | head -8; done
-for f in $O/*.pytest; do echo "== $f"; tail -2 $f; done
+if [ "$TOOL" = memcheck ]; then
+  SEL='tests/test_gpu_edges.py tests/test_gpu_output.py'; K='not 1920 and not grid1m and not c1_'
+  EXTRA="--leak-check no"
+else
+  SEL='tests/test_gpu_edges.py'; K='ragged or mirror or bounce or duplicate'
+  EXTRA=""
+  [ "$TOOL" = racecheck ] && EXTRA="--racecheck-report all"
+fi
+timeout 1500 compute-sanitizer --tool $TOOL $EXTRA --error-exitcode 9 --log-file $O/$TOOL.log python -m pytest $SEL -q -m gpu -x -p no:cacheprovider -k "$K" > $O/$TOOL.pytest 2>&1; echo "$TOOL rc=$?"
+echo "== $TOOL log"; grep -E "ERROR SUMMARY|RACECHECK SUMMARY|hazard|Invalid|Error|error" $O/$TOOL.log | sort | uniq -c | sort -rn | head -12
+echo "== pytest"; tail -3 $O/$TOOL.pytest
