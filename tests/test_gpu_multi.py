@@ -181,6 +181,7 @@ def test_set_gpus_tile_split_in_one_process_is_bitwise_the_one_gpu_frame(ptb):
     def render(n_gpus, accel, pipe, launches, scene_name):
         ptb.set_accel(accel); ptb.set_math(capi.MATH_PARITY); ptb.set_pipeline(pipe)
         ptb.set_gpus(n_gpus, capi.SPLIT_TILE)
+        ptb.reset_counters()                         # (after set_gpus: every participating GPU's counters)
         try:
             if scene_name == "cornell":
                 s = _scene(ptb)
