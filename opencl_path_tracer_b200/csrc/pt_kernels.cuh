@@ -726,7 +726,8 @@ __global__ void __launch_bounds__(PT_BLOCK, MINB) k_render(const RenderParams p)
         // on Cornell, profiles/r01_render_v7.txt); a waiting lane rides through the scan predicated off meanwhile
         const bool waiting = !alive && s < s_end;
         const int n_wait = __popc(__ballot_sync(0xffffffffu, waiting));
-        if (waiting && (n_wait >= p.regen_min || !__any_sync(0xffffffffu, alive))) {
+        const bool any_alive = __any_sync(0xffffffffu, alive);     // (both votes by the whole warp, outside the divergent test below)
+        if (waiting && (n_wait >= p.regen_min || !any_alive)) {
             if (p.from_rays) {                                   // drop-in trace_ray: gen_ray already ran
                 const float4 *r = reinterpret_cast<const float4 *>(p.rays + id);
                 rayP = v3(r[0]); rayD = v3(r[1]);

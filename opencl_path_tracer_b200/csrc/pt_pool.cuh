@@ -20,6 +20,11 @@
 //   * path state (throughputs, sample colour, accumulator, RNG: 6 float4) lives in global memory indexed by
 //     (warp, slot), touched only by the SHADE phase through L2 (ld.cg / st.cg: another lane of the warp may serve the
 //     slot next time).
+// MEASURED AND DROPPED (commit ac1d6e8, profiles/r02_pool_shards.txt): cutting every pixel's samples into chunks handed out chunk-major,
+// each chunk starting from the (RNG state, accumulator) its predecessor published in rnds[] / colors[], so that a GPU that owns only ~5
+// pixels per slot does not end with most slots idle during the last round of pixels: bit-identical, but 2570 vs 2733 Mrays/s on rank 0's
+// share of an 8-way tile split of the 4K frame and 3135 vs 3213 on the full 1080p frame — the extra per-item state reads, fences and
+// registers cost more than the shorter tail returns.
 // The traversal is the wavefront kernel's: 4-ary nodes, near/far planes picked by direction sign, 64-byte triangle
 // records, entry-distance culling at pop, closest hit = min (t, upload index).  Bit-identical to the other pipelines in
 // the parity flavour (tests/test_gpu_pool.py).
@@ -37,15 +42,13 @@
 #endif
 #define POOL_WARPS 4
 #define POOL_DEEP (PT_LBVH_STACK - POOL_STACK)
-enum { PL_DEAD = 0, PL_NODE = 1, PL_POP = 2, PL_LEAF = 3, PL_SHADE = 4, PL_EMPTY = 5, PL_WAIT = 6 };
+enum { PL_DEAD = 0, PL_NODE = 1, PL_POP = 2, PL_LEAF = 3, PL_SHADE = 4, PL_EMPTY = 5 };
 enum { PW_PX = 0, PW_PY, PW_PZ, PW_DX, PW_DY, PW_DZ, PW_IX, PW_IY, PW_IZ, PW_BT, PW_BTRI, PW_LINK, PW_SP, PW_PIX, PW_TAG, PW_FIELDS };
 #define POOL_WORDS (PW_FIELDS * POOL_NS + 2 * POOL_STACK * POOL_NS + 32)       // 32-bit words of shared memory per warp
 
 struct PoolArgs {
     int *cursor;                 // next item (owned pixel / ray of the list) to hand out; zeroed before the launch
     int n_items;
-    // sample chunks (launch_pool): item k = chunk k / n_owned of the (k % n_owned)-th owned pixel, chunk_spp samples each; n_chunks == 1: whole pixels
-    int n_owned, n_chunks, chunk_spp;
     int2 *deep;                  // stack overflow, POOL_DEEP entries per slot
     float4 *state;               // WF_PLANES planes of total_slots float4
     int total_slots;
@@ -124,22 +127,17 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
         const int t0 = PI(PW_TAG, lane);
         const int t1 = lane + 32 < POOL_NS ? PI(PW_TAG, (lane + 32) % POOL_NS) : PL_DEAD;
         const bool isN0 = t0 == PL_NODE || t0 == PL_POP, isN1 = t1 == PL_NODE || t1 == PL_POP;
-        const bool isL0 = t0 == PL_LEAF, isL1 = t1 == PL_LEAF, isS0 = t0 == PL_SHADE || t0 == PL_EMPTY, isS1 = t1 == PL_SHADE || t1 == PL_EMPTY;
-        const bool isW0 = t0 == PL_WAIT, isW1 = t1 == PL_WAIT;
-        const unsigned counts = __reduce_add_sync(full, (unsigned)(isN0 + isN1) | ((unsigned)(isL0 + isL1) << 8) | ((unsigned)(isS0 + isS1) << 16) |
-                                                            ((unsigned)(isW0 + isW1) << 24));   // one REDUX
-        const int cN = counts & 0xff, cL = (counts >> 8) & 0xff, cS = (counts >> 16) & 0xff;
+        const bool isL0 = t0 == PL_LEAF, isL1 = t1 == PL_LEAF, isS0 = t0 >= PL_SHADE, isS1 = t1 >= PL_SHADE;
+        const unsigned counts = __reduce_add_sync(full, (unsigned)(isN0 + isN1) | ((unsigned)(isL0 + isL1) << 8) | ((unsigned)(isS0 + isS1) << 16));   // one REDUX
+        const int cN = counts & 0xff, cL = (counts >> 8) & 0xff, cS = counts >> 16;
         if (counts == 0u) break;                      // every slot is dead: no pixels left
         int phase;                                    // 0 node, 1 leaf, 2 shade
         if (cN >= 32) phase = 0;
         else if (cL >= a.leaf_min) phase = 1;
         else if (cS >= a.shade_min) phase = 2;
         else phase = (cN >= cL && cN >= cS) ? 0 : (cL >= cS ? 1 : 2);
-        // slots waiting for the previous sample chunk of their pixel (rare: see launch_pool) are looked at only when nothing else is runnable
-        const bool only_waiting = (counts & 0xffffffu) == 0u;
-        if (only_waiting) phase = 2;
-        const unsigned m0 = __ballot_sync(full, only_waiting ? isW0 : (phase == 0 ? isN0 : (phase == 1 ? isL0 : isS0)));
-        const unsigned m1 = __ballot_sync(full, only_waiting ? isW1 : (phase == 0 ? isN1 : (phase == 1 ? isL1 : isS1)));
+        const unsigned m0 = __ballot_sync(full, phase == 0 ? isN0 : (phase == 1 ? isL0 : isS0));
+        const unsigned m1 = __ballot_sync(full, phase == 0 ? isN1 : (phase == 1 ? isL1 : isS1));
         const int c0 = __popc(m0);
         if ((m0 >> lane) & 1u) sel[__popc(m0 & lt)] = lane;
         if ((m1 >> lane) & 1u) { const int r = c0 + __popc(m1 & lt); if (r < 32) sel[r] = lane + 32; }
@@ -288,8 +286,7 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
             // -------------------------------------------------------- SHADE: finished rays -> next ray of the path / next sample / next pixel
             const int tg = active ? PI(PW_TAG, slot) : PL_DEAD;
             const int gslot = gwarp * POOL_NS + slot;
-            const bool chunked = MODE == 0 && a.n_chunks > 1;
-            int pix = -1, chunk = 0;                  // the slot's item: pixel and sample chunk (word PW_PIX = pixel | chunk << 24 when chunked)
+            int pix = -1;
             WfPath w;
             w.rng = 1u; w.acc = v3(0.0f, 0.0f, 0.0f); w.s = s_end; w.depth = 0;
             path_reset(w.ps);
@@ -297,15 +294,8 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
             bool has = false;                         // the slot leaves this phase with a ray to trace
             bool want_sample = false;                 // ... needs the next sample of its pixel started (or the pixel finished)
             bool want_pixel = active && tg == PL_EMPTY;
-            bool want_start = false;                  // ... has an item whose per-pixel state is still to be read (and, chunk > 0, may not be ready yet)
-            bool waiting = false;
-            if (tg == PL_SHADE || tg == PL_WAIT) {
-                const int item = PI(PW_PIX, slot);
-                pix = chunked ? item & 0xffffff : item;
-                chunk = chunked ? (int)((unsigned)item >> 24) : 0;
-                want_start = tg == PL_WAIT;
-            }
             if (tg == PL_SHADE) {
+                pix = PI(PW_PIX, slot);
                 const float t = PF(PW_BT, slot);
                 const int tri = PI(PW_BTRI, slot);
                 if (MODE == 1) {
@@ -351,35 +341,19 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
                             pix = k;
                             has = true;
                         } else {
-                            chunk = chunked ? k / a.n_owned : 0;
-                            pix = pool_item_pixel(p, k - chunk * a.n_owned);
-                            want_start = true;
+                            pix = pool_item_pixel(p, k);
+                            w.rng = (uint32_t)p.rnds[pix];
+                            w.acc = (p.sample0 != 0 || p.sum_mode) ? v3(p.colors[pix]) : v3(0.0f, 0.0f, 0.0f);
+                            w.s = p.sample0;
+                            want_sample = true;
                         }
                     }
                 }
                 if (MODE == 1) { if (need == 0u) break; continue; }
-                if (want_start) {
-                    // the pixel's state at the start of this item.  Chunk c > 0 continues where chunk c - 1 (possibly on another warp or SM)
-                    // left off: that one published (acc, c) in colors[pix] AFTER the RNG state; until then the slot waits (tag PL_WAIT)
-                    want_start = false;
-                    bool ready = true;
-                    if (chunk > 0) {
-                        const float4 v = __ldcg(p.colors + pix);
-                        ready = __float_as_int(v.w) == chunk;
-                        if (ready) { w.acc = v3(v); __threadfence_system(); w.rng = (uint32_t)__ldcg(p.rnds + pix); }
-                    } else {
-                        w.rng = (uint32_t)p.rnds[pix];
-                        w.acc = (p.sample0 != 0 || p.sum_mode) ? v3(p.colors[pix]) : v3(0.0f, 0.0f, 0.0f);
-                    }
-                    w.s = p.sample0 + chunk * a.chunk_spp;
-                    want_sample = ready;
-                    waiting = !ready;
-                }
                 if (!__any_sync(full, want_sample)) { if (need == 0u) break; continue; }
                 if (want_sample) {
                     want_sample = false;
-                    const int my_end = chunked ? min(s_end, p.sample0 + (chunk + 1) * a.chunk_spp) : s_end;
-                    if (w.s < my_end) {                                          // gen_ray, prog.cl:384-389
+                    if (w.s < s_end) {                                           // gen_ray, prog.cl:384-389
                         const int camX = max((int)p.cam.XM, 1);
                         const float r1 = pt_rand(w.rng), r2 = pt_rand(w.rng);
                         camera_ray(p, pix % camX, pix / camX, r1, r2, rayP, rayD);
@@ -393,18 +367,12 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
                             want_sample = true;
                         }
                     } else {
-                        if (my_end >= s_end) wf_finish_pixel(p, pix, w);
-                        else {                                                   // end of a chunk: hand the pixel's state to whoever runs the next one
-                            p.rnds[pix] = (int)w.rng;
-                            __threadfence_system();
-                            __stcg(p.colors + pix, make_float4(w.acc.x, w.acc.y, w.acc.z, __int_as_float(chunk + 1)));
-                        }
+                        wf_finish_pixel(p, pix, w);
                         pix = -1;
                         want_pixel = true;
                     }
                 }
             }
-            if (only_waiting && !__any_sync(full, has)) __nanosleep(500);         // nothing became ready: do not hammer L2
             if (active) {
                 if (has) {
                     Closest best;
@@ -414,12 +382,9 @@ __global__ void __launch_bounds__(32 * POOL_WARPS, POOL_MINB) k_pool(const Rende
                     PF(PW_DX, slot) = rayD.x; PF(PW_DY, slot) = rayD.y; PF(PW_DZ, slot) = rayD.z;
                     PF(PW_IX, slot) = pool_rcp(rayD.x); PF(PW_IY, slot) = pool_rcp(rayD.y); PF(PW_IZ, slot) = pool_rcp(rayD.z);
                     PF(PW_BT, slot) = best.t; PI(PW_BTRI, slot) = best.tri;
-                    PI(PW_LINK, slot) = sc.bvh_root; PI(PW_SP, slot) = 0; PI(PW_PIX, slot) = chunked ? (pix | (chunk << 24)) : pix;
+                    PI(PW_LINK, slot) = sc.bvh_root; PI(PW_SP, slot) = 0; PI(PW_PIX, slot) = pix;
                     PI(PW_TAG, slot) = sc.bvh_root >= 0 ? PL_NODE : PL_LEAF;
                     if (MODE == 0) pool_store_state(a, gslot, w);
-                } else if (waiting) {
-                    PI(PW_PIX, slot) = pix | (chunk << 24);
-                    PI(PW_TAG, slot) = PL_WAIT;
                 } else {
                     PI(PW_TAG, slot) = PL_DEAD;
                 }
@@ -504,22 +469,7 @@ int launch_pool(const RenderParams &p, void *scratch, cudaStream_t st) {
     if (items <= 0) return 0;
     const bool qn = p.sc.bvh4q != nullptr;
     const PoolPlan pl = p.count_work ? (qn ? pool_plan_t<true, 0, true>() : pool_plan_t<true, 0, false>()) : (qn ? pool_plan_t<false, 0, true>() : pool_plan_t<false, 0, false>());
-    PoolArgs a = pool_args(pl, scratch, (int)items);
-    // Sample chunks.  A slot keeps its pixel for all its samples (they are sequential), so a GPU that owns only a few pixels per slot
-    // (one rank of an 8-way tile split of a 4K frame: 5.2) ends with most slots idle while the last round of pixels runs its whole
-    // lifetime — 13 % of the render at 5.2 rounds.  Cutting every pixel's samples into chunks that are handed out chunk-major (all first
-    // chunks, then all second chunks ...) makes the rounds that much shorter; a chunk starts from the state its predecessor published.
-    static const int want_rounds = getenv("PTB_POOL_ROUNDS") ? atoi(getenv("PTB_POOL_ROUNDS")) : 32;
-    a.n_owned = (int)items; a.n_chunks = 1; a.chunk_spp = p.spp;
-    if (want_rounds > 0 && n < (1 << 24) && items >= 2LL * pl.total_slots && items < (long long)want_rounds * pl.total_slots && p.spp > 1) {
-        long long nc = ((long long)want_rounds * pl.total_slots + items - 1) / items;
-        if (nc > p.spp) nc = p.spp;
-        if (nc > 127) nc = 127;
-        a.chunk_spp = (int)((p.spp + nc - 1) / nc);
-        a.n_chunks = (p.spp + a.chunk_spp - 1) / a.chunk_spp;
-        if ((long long)a.n_chunks * items < (1LL << 31)) a.n_items = (int)(a.n_chunks * items);
-        else { a.n_chunks = 1; a.chunk_spp = p.spp; }
-    }
+    const PoolArgs a = pool_args(pl, scratch, (int)items);
     cudaMemsetAsync(a.cursor, 0, sizeof(int), st);
     // no more blocks than there are items to start on (a 16x16 frame does not need 1000 idle blocks)
     long long blocks = (items + POOL_WARPS * POOL_NS - 1) / (POOL_WARPS * POOL_NS);
