@@ -207,6 +207,16 @@ int ptb_resolve_rgba8(ptb_mem colors, int width, int height, int mode, unsigned 
  * writes to its texture, prog.cl:380) and the 8-bit RGBA picture into dst_host (NULL = none; as ptb_resolve_rgba8).  The tone
  * map keeps prog.cl's operations and order (no FMA contraction, pow as the correctly rounded float of the double function). */
 int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int mode, ptb_mem image, unsigned char *dst_host);
+/* ptb_resolve_rgba8 WITHOUT ANY ALLOCATION.  No counterpart in the reference; added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and the
+ * same picture as ptb_resolve_rgba8; the device-side staging buffer is a static __device__ array of PTB_NOALLOC_MAX_PIXELS * 4 bytes
+ * (8 MiB; every GPU that loads the library holds it until exit) instead of a per-call cudaMalloc.  width * height beyond
+ * PTB_NOALLOC_MAX_PIXELS is rejected with PTB_ERR_INVALID_VALUE (use ptb_resolve_rgba8 then).  The call makes no cudaMalloc, cudaFree
+ * or allocating library call; like ptb_resolve_rgba8 it returns when dst_host is filled.  Every call shares the one array, which keeps
+ * the previous call's contents (each call overwrites all of the width * height pixels it uses, nothing needs clearing): calls that
+ * overlap on the GPU — other host threads, other processes' streams are fine, other streams of THIS process are not — race. */
+#define PTB_NOALLOC_MAX_PIXELS (2 * 1024 * 1024)
+int ptb_resolve_rgba8_noalloc(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host);
 /* 3x3 median denoise of prog.cl:391-427 as a standalone pass: colors → image (RGBA float). */
 int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height);
 

@@ -24,7 +24,7 @@ SYMBOLS = [
     "ptb_reset_counters", "ptb_resolve_rgba8", "ptb_filter_median", "ptb_set_stream", "ptb_get_stream",
     "ptb_accel_stats", "ptb_launch_count", "ptb_closest_hit", "ptb_invalidate", "ptb_resolve_frame", "ptb_save_state", "ptb_load_state",
     "ptb_comm_unique_id", "ptb_comm_init", "ptb_comm_ranks", "ptb_comm_rank", "ptb_comm_reduce", "ptb_comm_broadcast", "ptb_comm_barrier", "ptb_comm_destroy",
-    "ptb_set_gpus", "ptb_get_gpus", "ptb_set_quant_nodes",
+    "ptb_set_gpus", "ptb_get_gpus", "ptb_set_quant_nodes", "ptb_resolve_rgba8_noalloc",
 ]
 
 
@@ -74,7 +74,7 @@ def load_library(path=None):
         "ptb_invalidate": (i, [u64]), "ptb_resolve_frame": (i, [u64, i, i, i, i, u64, vp]),
         "ptb_save_state": (i, [cp]), "ptb_load_state": (i, [cp, C.POINTER(i)]),
         "ptb_comm_unique_id": (i, [vp]), "ptb_comm_init": (i, [i, i, vp]), "ptb_comm_ranks": (i, []), "ptb_comm_rank": (i, []),
-        "ptb_set_quant_nodes": (i, [i]), "ptb_set_gpus": (i, [i, i]), "ptb_get_gpus": (i, []),
+        "ptb_resolve_rgba8_noalloc": (i, [u64, i, i, i, vp]), "ptb_set_quant_nodes": (i, [i]), "ptb_set_gpus": (i, [i, i]), "ptb_get_gpus": (i, []),
         "ptb_comm_reduce": (i, [u64, i]), "ptb_comm_broadcast": (i, [u64, i]), "ptb_comm_barrier": (i, []), "ptb_comm_destroy": (i, []),
     }
     for name, (res, args) in proto.items():
@@ -265,6 +265,14 @@ class Ptb:
     def resolve_rgba8(self, colors, w, h, mode=0):
         out = np.empty((h, w, 4), dtype=np.uint8)
         self._ck(self.lib.ptb_resolve_rgba8(colors, w, h, mode, out.ctypes.data), "ptb_resolve_rgba8")
+        return out
+
+    def resolve_rgba8_noalloc(self, colors, w, h, mode=0, out=None):
+        """ptb_resolve_rgba8_noalloc: the same picture through the static device scratch (no allocation on the library side);
+        `out` lets the caller bring its own (h, w, 4) uint8 array so that nothing is allocated on this side either"""
+        if out is None:
+            out = np.empty((h, w, 4), dtype=np.uint8)
+        self._ck(self.lib.ptb_resolve_rgba8_noalloc(colors, w, h, mode, out.ctypes.data), "ptb_resolve_rgba8_noalloc")
         return out
 
     def resolve_frame(self, colors, w, h, divide_by=1, mode=0, image=0, want_rgba8=True):

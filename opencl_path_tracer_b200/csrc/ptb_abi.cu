@@ -24,6 +24,7 @@
 #include "pt_params.h"
 #include "ptb200.h"
 #include "resolve.h"
+static_assert(PTB_NOALLOC_MAX_PIXELS == RESOLVE_NOALLOC_MAX_PIXELS, "ptb200.h and resolve.h disagree on the static scratch size");
 
 namespace {
 
@@ -1309,6 +1310,23 @@ int ptb_resolve_frame(ptb_mem colors, int width, int height, int divide_by, int 
     if (e == cudaSuccess && dst_host) e = cudaStreamSynchronize(S());
     cudaFree(d);
     if (e != cudaSuccess) return fail(PTB_ERR_DEVICE, "ptb_resolve_frame: %s", cudaGetErrorString(e));
+    return PTB_SUCCESS;
+}
+// ptb_resolve_rgba8 for callers that must not allocate: same arguments, same picture, the staging buffer is a static device array
+// (resolve.cu).  No cudaMalloc / cudaFree / allocating library call on this path.
+int ptb_resolve_rgba8_noalloc(ptb_mem colors, int width, int height, int mode, unsigned char *dst_host) {
+    NEED_INIT();
+    MemObj *m = find(colors);
+    const size_t n = (size_t)(width > 0 ? width : 0) * (size_t)(height > 0 ? height : 0);
+    if (!m || !dst_host || n == 0 || m->bytes / 16 < n || (mode != 0 && mode != 1)) return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_rgba8_noalloc: bad arguments");
+    if (n > (size_t)PTB_NOALLOC_MAX_PIXELS)
+        return fail(PTB_ERR_INVALID_VALUE, "ptb_resolve_rgba8_noalloc: %d x %d pixels exceed the static scratch of PTB_NOALLOC_MAX_PIXELS = %d pixels; use ptb_resolve_rgba8",
+                    width, height, PTB_NOALLOC_MAX_PIXELS);
+    int rc = flush_pending();
+    if (rc) return rc;
+    char err[256];
+    if (resolve_rgba8_noalloc((const float4 *)m->dptr, width, height, mode, dst_host, S(), err, sizeof err)) return fail(PTB_ERR_DEVICE, "%s", err);
+    G.launches++;
     return PTB_SUCCESS;
 }
 int ptb_filter_median(ptb_mem colors, ptb_mem image, int width, int height) {

@@ -10,6 +10,7 @@
 //                   pixel is read 1.3x instead of 9x), 19-exchange median network on (grey, slot) pairs, and the
 //                   reference's literal selection sort only where its tie handling could matter
 #include "resolve.h"
+#include <stdio.h>
 
 namespace {
 
@@ -124,6 +125,42 @@ void resolve_frame(const ResolveSrc &src, float scale, int w, int h, int mode, f
     if (blocks > 148 * 32) blocks = 148 * 32;         // grid-stride over a multiple of the SM count
     k_resolve<<<(unsigned)blocks, 256, 0, st>>>(src, scale, w, h, mode, mean_out, tex_out, (uchar4 *)rgba_out);
 }
+// ---------------------------------------------------------------- the resolve without any allocation (ptb_resolve_rgba8_noalloc)
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the 8-bit
+// picture is staged in a file-scope device array instead of a per-call cudaMalloc'ed buffer.  Every GPU that loads the library holds
+// the array (RESOLVE_NOALLOC_MAX_PIXELS * 4 bytes = 8 MiB) until exit.  ALL calls share it and it keeps the last call's contents: the
+// kernel writes every one of the w * h pixels it is asked for, so nothing has to start at zero; calls that overlap on the GPU race.
+// In host code `g_noalloc_rgba` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) unsigned char g_noalloc_rgba[(size_t)RESOLVE_NOALLOC_MAX_PIXELS * 4];
+
+int resolve_rgba8_noalloc(const float4 *colors, int w, int h, int mode, unsigned char *dst_host, cudaStream_t st, char *err, size_t errcap) {
+    static unsigned char *dev_ptr[64] = {};          // per device ordinal
+    const size_t n = (size_t)w * h;
+    if (n == 0 || n > (size_t)RESOLVE_NOALLOC_MAX_PIXELS) {
+        snprintf(err, errcap, "resolve without allocation: %d x %d = %zu pixels, the static scratch holds at most %d", w, h, n, RESOLVE_NOALLOC_MAX_PIXELS);
+        return -1;
+    }
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) { snprintf(err, errcap, "resolve without allocation: cudaGetDevice: %s", cudaGetErrorString(e)); return -1; }
+    if (!dev_ptr[dev]) {                              // set-up, once per device, with that device current
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_noalloc_rgba);
+        if (e != cudaSuccess || !ptr) { snprintf(err, errcap, "resolve without allocation: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return -1; }
+        dev_ptr[dev] = (unsigned char *)ptr;
+    }
+    ResolveSrc src{};
+    src.p[0] = colors; src.n = 1;
+    size_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    k_resolve<<<(unsigned)blocks, 256, 0, st>>>(src, 1.0f, w, h, mode, nullptr, nullptr, (uchar4 *)dev_ptr[dev]);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dst_host, dev_ptr[dev], n * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { snprintf(err, errcap, "resolve without allocation: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
 void filter_median(const float4 *colors, float4 *image, int w, int h, cudaStream_t st) {
     k_median<<<dim3((w + MED_BX - 1) / MED_BX, (h + MED_BY - 1) / MED_BY), dim3(MED_BX, MED_BY), 0, st>>>(colors, image, w, h);
 }
