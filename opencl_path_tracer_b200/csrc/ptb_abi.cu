@@ -138,7 +138,7 @@ struct State {
     int brute_max = 64;                // AUTO: brute force from shared memory up to this many triangles
     unsigned long long launches = 0;
     PendingGen pending;
-    int regen_min = 1;                 // k_render: batch path regeneration until this many lanes of a warp wait (PTB_REGEN_MIN)
+    int regen_min = 8;                 // k_render: batch path regeneration until this many lanes of a warp wait (PTB_REGEN_MIN)
     int quant_nodes = 1;               // pool kernel: traverse the 64-byte quantised wide nodes (PTB_QUANT_NODES=0: the 128-byte float nodes)
     int auto_pool = 2;                 // PTB_PIPE_AUTO on LBVH scenes: 0 = the wavefront, 1 = the pool kernel, 2 = by owned pixels (PTB_AUTO_POOL)
     long long auto_pool_pixels = 1500000;   // ... the pool kernel up to this many pixels on this GPU (PTB_AUTO_POOL_PIXELS)
