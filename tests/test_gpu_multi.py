@@ -252,7 +252,8 @@ def test_set_gpus_spp_split_in_one_process_converges_and_resolves(ptb):
     for i in idx:
         want = np.zeros(4, dtype=np.float32)
         fn(flat_c[i].ctypes.data, want.ctypes.data)
-        assert want.view(np.uint32).tolist() == flat_t[i].view(np.uint32).tolist()
+        same = (want.view(np.uint32) == flat_t[i].view(np.uint32)) | (np.isnan(want) & np.isnan(flat_t[i]))      # L == 0: a NaN, whichever payload
+        assert same.all(), (i, want, flat_t[i])
 
 
 def test_reference_host_renders_on_two_gpus_through_the_c_abi(tmp_path):
