@@ -553,6 +553,10 @@ struct Carver {
 struct Scratch {
     unsigned *bounds; unsigned long long *keys, *keys2; int *vals, *vals2, *pleaf, *arrivals, *stats;
     void *sort_tmp, *scan_tmp;
+    // PLOC: two cluster lists (lo | code, hi | size), the round's flags' prefix sums, subtree sizes, the tree-order permutation
+    float4 *clo[2], *chi[2];
+    unsigned long long *pscan;
+    int *size, *vals3, *pleaf2;
 };
 // the layout is a function of the capacity alone, so the pointers stay put across rebuilds
 size_t lbvh_carve(Lbvh *b, Scratch &t, char *base, size_t cap, size_t sort_bytes, size_t scan_bytes) {
@@ -568,6 +572,8 @@ size_t lbvh_carve(Lbvh *b, Scratch &t, char *base, size_t cap, size_t sort_bytes
     t.bounds = c.take<unsigned>(8); t.keys = c.take<unsigned long long>(cap); t.keys2 = c.take<unsigned long long>(cap);
     t.vals = c.take<int>(cap); t.vals2 = c.take<int>(cap); t.pleaf = c.take<int>(cap); t.arrivals = c.take<int>(cap); t.stats = c.take<int>(4);
     t.sort_tmp = c.take<char>(sort_bytes); t.scan_tmp = c.take<char>(scan_bytes);
+    for (int k = 0; k < 2; ++k) { t.clo[k] = c.take<float4>(cap); t.chi[k] = c.take<float4>(cap); }
+    t.pscan = c.take<unsigned long long>(cap); t.size = c.take<int>(cap); t.vals3 = c.take<int>(cap); t.pleaf2 = c.take<int>(cap);
     return c.off + 256;
 }
 }  // namespace
@@ -621,6 +627,11 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     size_t sort_bytes = 0, scan_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (unsigned long long *)nullptr, (unsigned long long *)nullptr, (int *)nullptr, (int *)nullptr, cap, 0, 64, st));
     CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int *)nullptr, (int *)nullptr, cap, st));
+    {
+        size_t scan64 = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, scan64, (unsigned long long *)nullptr, (unsigned long long *)nullptr, cap, st));
+        if (scan64 > scan_bytes) scan_bytes = scan64;
+    }
     if (!b->arena) {
         const size_t bytes = lbvh_carve(b, t, nullptr, (size_t)cap, sort_bytes, scan_bytes);
         CK(cudaMalloc(&b->arena, bytes));
@@ -659,11 +670,59 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
     CK(cudaMemcpyAsync(b->sorted_id, vals2, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
     b->launches += 1;
     if (m >= 2) {
-        CK(cudaMemsetAsync(arrivals, 0, (size_t)n * sizeof(int), st));
-        k_hierarchy<<<grid, 256, 0, st>>>(keys2, m, (int2 *)b->range, (int2 *)b->child, pnode, pleaf);
-        k_refit<<<grid, 256, 0, st>>>(m, (const int2 *)b->child, pnode, pleaf, b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, arrivals);
+        static const int use_ploc = getenv("PTB_LBVH_PLOC") ? atoi(getenv("PTB_LBVH_PLOC")) : 1;
+        bool ploc_done = false;
+        b->ploc_rounds = 0;
+        if (use_ploc) {
+            // ---- PLOC rounds over the Morton-ordered triangles [0, m); keys (the unsorted codes) and vals are free after the sort: flags and nn
+            unsigned long long *flags = keys;
+            int *nn = vals;
+            k_ploc_init<<<(m + 255) / 256, 256, 0, st>>>(m, b->leaf_lo, b->leaf_hi, t.clo[0], t.chi[0]);
+            int cur = 0, mc = m, next_id = m - 2, rounds = 0;
+            unsigned long long h_last[2];
+            while (mc > 1 && rounds < 1024) {
+                const int g = (mc + 255) / 256;
+                k_ploc_nn<<<g, 256, 0, st>>>(mc, t.clo[cur], t.chi[cur], nn);
+                k_ploc_flag<<<g, 256, 0, st>>>(mc, nn, flags);
+                CK(cub::DeviceScan::ExclusiveSum(t.scan_tmp, scan_bytes, flags, t.pscan, mc, st));
+                k_ploc_apply<<<g, 256, 0, st>>>(mc, next_id, nn, flags, t.pscan, t.clo[cur], t.chi[cur], t.clo[cur ^ 1], t.chi[cur ^ 1], (int2 *)b->child,
+                                                b->node_lo, b->node_hi, t.size, pnode, pleaf);
+                CK(cudaMemcpyAsync(&h_last[0], flags + (mc - 1), 8, cudaMemcpyDeviceToHost, st));
+                CK(cudaMemcpyAsync(&h_last[1], t.pscan + (mc - 1), 8, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                const unsigned long long tot = h_last[0] + h_last[1];
+                const int kept = (int)(tot & 0xffffffffull), merged = (int)(tot >> 32);
+                b->launches += 5;
+                ++rounds;
+                if (merged < 1 || kept != mc - merged) break;           // cannot happen (see k_ploc_nn); the radix tree takes over
+                next_id -= merged;
+                mc = kept;
+                cur ^= 1;
+            }
+            if (mc == 1 && next_id == -1) {
+                // ---- tree order: positions, ranges, remapped leaf links; the triangles are gathered again in that order below
+                const int root_parent = -1;
+                CK(cudaMemcpyAsync(pnode, &root_parent, sizeof(int), cudaMemcpyHostToDevice, st));      // node 0 is the root
+                k_ploc_newpos<<<grid, 256, 0, st>>>(m, (const int2 *)b->child, t.size, pnode, pleaf, arrivals);
+                k_ploc_range<<<grid, 256, 0, st>>>(m, (const int2 *)b->child, t.size, arrivals, (int2 *)b->range);
+                k_ploc_remap<<<grid, 256, 0, st>>>(m, n, arrivals, (int2 *)b->child, vals2, t.vals3, pleaf, t.pleaf2);
+                k_gather<<<grid, 256, 0, st>>>(q0, q1, q2, f0, f1, f2, t.vals3, n, b->sq0, b->sq1, b->sq2, b->sf0, b->sf1, b->sf2, b->leaf_lo, b->leaf_hi, b->rq, b->rf);
+                CK(cudaMemcpyAsync(b->sorted_id, t.vals3, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+                CK(cudaMemcpyAsync(pleaf, t.pleaf2, (size_t)m * sizeof(int), cudaMemcpyDeviceToDevice, st));
+                CK(cudaGetLastError());
+                b->launches += 4;
+                b->ploc_rounds = rounds;
+                ploc_done = true;
+            }
+        }
+        if (!ploc_done) {
+            CK(cudaMemsetAsync(arrivals, 0, (size_t)n * sizeof(int), st));
+            k_hierarchy<<<grid, 256, 0, st>>>(keys2, m, (int2 *)b->range, (int2 *)b->child, pnode, pleaf);
+            k_refit<<<grid, 256, 0, st>>>(m, (const int2 *)b->child, pnode, pleaf, b->leaf_lo, b->leaf_hi, b->node_lo, b->node_hi, arrivals);
+            b->launches += 2;
+        }
         k_depth<<<grid, 256, 0, st>>>(m, b->leaf_size, (const int2 *)b->range, pnode, pleaf, stats, stats + 1);
-        b->launches += 3;
+        b->launches += 1;
     }
     unsigned hb[8];
     int hs[4];

@@ -26,6 +26,7 @@ struct Lbvh {
     void *range, *child;          // int2 per internal node
     float4 *leaf_lo, *leaf_hi, *node_lo, *node_hi;
     int n_tris, leaf_size, n_nodes, max_depth;
+    int ploc_rounds;              // clustering rounds of the PLOC build (0: the Karras radix tree was used — PTB_LBVH_PLOC=0)
     int n_tree, n_big;            // Morton positions [0, n_tree) are under the tree, [n_tree, n_tris) is the outlier list
     float max_abs, reach, eps, build_ms;
     unsigned long long launches;
