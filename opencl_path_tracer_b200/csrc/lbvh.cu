@@ -432,9 +432,10 @@ __global__ void k_emit4(int n, int leaf_size, float eps, const int2 *range, cons
 //   w3    biased exponents ex | ey << 8 | ez << 16 of 128 * step (step = 2^k per axis, >= extent / 250)
 //   w4-9  per axis the four children's lower bounds (one byte each), then their upper bounds: x lo, x hi, y lo, y hi, z lo, z hi
 //   w12-15 links (same encoding as the 128-byte node)
-// A child's box is [p + qlo * step, p + qhi * step] with qlo = floor(..) - 1 and qhi = ceil(..) + 1: it contains the (already
-// eps-inflated) float box with a whole step to spare on every side, which covers the rounding of the decode in the
-// traversal (< 2^-8 step, see k_pool).  Empty slot: qlo = 255, qhi = 0 (inverted on every axis: never hit).
+// A child's box is [p + qlo * step, p + qhi * step] with qlo = floor(x - 2^-7) and qhi = ceil(x + 2^-7), x in steps from p: it contains
+// the (already eps-inflated) float box with 2^-7 of a step to spare on every side, which covers the rounding of x here and of the decode
+// in the traversal (< 2^-8 step, see k_pool).  (A whole step of slack, the first version, cost 7 % more box tests per ray.)
+// Empty slot: qlo = 255, qhi = 0 (inverted on every axis: never hit).
 __global__ void k_emit4q(int n, int leaf_size, float eps, const int2 *range, const int2 *child, const int *flag, const int *id4,
                          const float4 *leaf_lo, const float4 *leaf_hi, const float4 *node_lo, const float4 *node_hi, uint4 *bvh4q) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -469,15 +470,15 @@ __global__ void k_emit4q(int n, int leaf_size, float eps, const int2 *range, con
         frexpf(ext * (1.0f / 250.0f), &e2);                 // ext / 250 = m * 2^e2, m in [0.5, 1): step = 2^e2 >= ext / 250
         e2 = max(-120, min(120, e2));
         const float step = ldexpf(1.0f, e2), inv_step = ldexpf(1.0f, -e2);
-        const float p = ulo[a] - 2.0f * step;
+        const float p = ulo[a] - step;
         w[a] = __float_as_uint(p);
         exps |= (unsigned)(e2 + 7 + 127) << (8 * a);
         unsigned qlo = 0u, qhi = 0u;
         for (int k = 0; k < 4; ++k) {
             int ql = 255, qh = 0;
             if (k < ns) {
-                ql = (int)floorf((lo[k][a] - p) * inv_step) - 1;
-                qh = (int)ceilf((hi[k][a] - p) * inv_step) + 1;
+                ql = (int)floorf((lo[k][a] - p) * inv_step - 0.0078125f);      // 2^-7 of a step outward: covers the subtraction's rounding here
+                qh = (int)ceilf((hi[k][a] - p) * inv_step + 0.0078125f);       // (<= 2^-16 step) and the decode's in the traversal (< 2^-8 step)
                 ql = max(0, min(255, ql)); qh = max(0, min(255, qh));
             }
             qlo |= (unsigned)ql << (8 * k); qhi |= (unsigned)qh << (8 * k);
