@@ -137,9 +137,10 @@ int ptb_set_pipeline(int pipe);
 /* wavefront pipeline: number of interleaved sub-wavefronts (independent ray queues on separate streams that fill each
  * other's trace tails), 1..4, default 2 (env PTB_WF_SUBS).  The image does not depend on it. */
 int ptb_set_wf_subs(int n);
-/* pool kernel: read the LBVH's 4-ary nodes in their 64-byte quantised form (8-bit child boxes against the node's own origin and
- * power-of-two step, rounded outward by a whole step: conservative, so the closest hit is unchanged) — two 256-bit loads per
- * node instead of five fetches of the 128-byte float node.  Default 1 (env PTB_QUANT_NODES).  The image does not depend on it. */
+/* LBVH traversal (wavefront and pool kernel): read the 4-ary nodes in their 64-byte quantised form (8-bit child boxes against the node's
+ * own origin and power-of-two step, rounded outward: conservative, so the closest hit is unchanged) — four 16-byte fetches per node
+ * instead of five fetches of the 128-byte float node.  0 = never, 1 = always (both pipelines), 2 (default) = the pool kernel when the
+ * float nodes exceed 8 MB, the wavefront never (both by measurement; env PTB_QUANT_NODES).  The image does not depend on it. */
 int ptb_set_quant_nodes(int on);
 /* The reference enqueues gen_ray then trace_ray for every sample (main.cpp:683-687).  With fusion on
  * (the default) a gen_ray launch is deferred and folded into the trace_ray launch that follows it on

@@ -937,10 +937,11 @@ int launch_closest_hit(const RenderParams &p0, const RefRay *rays, size_t n, flo
         int sms = 148, dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+        const int wide = wf_wide_mode(p.sc);
         const int3 tune = make_int3(WF_FETCH_MIN, 4, PT_SCHED_NODE_STEPS);
-        if (wide) k_wf_trace<false, true><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
-        else k_wf_trace<false, false><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
+        if (wide == 2) k_wf_trace<false, 2><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
+        else if (wide == 1) k_wf_trace<false, 1><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
+        else k_wf_trace<false, 0><<<sms * 8, PT_BLOCK, 0, st>>>(p, p.wf_queue[0], p.wf_ctrl, p.wf_ctrl + 2, tune);
         k_ch_unpack<<<blocks, 128, 0, st>>>(p.wf_ray1, n, out);
         return 3;
     }

@@ -35,6 +35,7 @@ struct SceneDev {
     cudaTextureObject_t bvh_tex, bvh4_tex;   // bvh / bvh4 as linear float4 textures, 0 = fetch through the LSU
     cudaTextureObject_t bvh4q_tex;           // bvh4q as a linear uint4 texture, 0 = fetch through the LSU
     const float4 *bvh4q;          // the 4-ary nodes quantised to 64 bytes (lbvh.cu k_emit4q); null: traverse the float nodes
+    int quant_wf;                 // 1: the wavefront's trace kernel walks them too (forced by ptb_set_quant_nodes(1); by measurement it prefers the float nodes)
     const float4 *bvh4;           // the same tree collapsed to 4-ary nodes, 8 float4 each (lbvh.cu); null: not usable
     const float4 *sq0, *sq1, *sq2;// triangles in Morton order
     const int *sorted_id;         // Morton position → index in upload order

@@ -285,7 +285,8 @@ enum { WF_FETCH = 0, WF_NODE = 1, WF_LEAF = 2, WF_EXIT = 3, WF_POP = 4 };
 #ifndef WF_MINB
 #define WF_MINB 8                 // resident blocks per SM the register allocation is held to
 #endif
-template <bool COUNT, bool WIDE>
+// WIDE: 0 = binary nodes, 1 = 4-ary float nodes (128 bytes), 2 = 4-ary quantised nodes (64 bytes, lbvh.cu k_emit4q)
+template <bool COUNT, int WIDE>
 __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderParams p, const int *q_in, const int *n_in, int *cursor, const int3 tune) {
     const SceneDev &sc = p.sc;
     const int lane = threadIdx.x & 31;
@@ -331,6 +332,9 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     const float4 r0 = p.wf_ray0[path], r1 = p.wf_ray1[path];
                     P = v3(r0.x, r0.y, r0.z); D = v3(r0.w, r1.x, r1.y);
                     ix = safe_rcp(D.x); iy = safe_rcp(D.y); iz = safe_rcp(D.z);
+                    if (WIDE == 2) {                                   // bounded, so that 128 * step * (1 / d) of the quantised decode cannot overflow
+                        ix = fminf(fmaxf(ix, -1e25f), 1e25f); iy = fminf(fmaxf(iy, -1e25f), 1e25f); iz = fminf(fmaxf(iz, -1e25f), 1e25f);
+                    }
                     ox = P.x * ix; oy = P.y * iy; oz = P.z * iz;
                     nx = ix < 0.0f ? 1 : 0; ny = iy < 0.0f ? 1 : 0; nz = iz < 0.0f ? 1 : 0;
                     best.t = r1.z; best.tri = __float_as_int(r1.w);        // the outlier scan ran where the ray was created (wf_big_scan)
@@ -365,7 +369,51 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                         }
                     }
                 }
-                if (WIDE && st == WF_NODE) {
+                if (WIDE == 2 && st == WF_NODE) {
+                    // quantised wide node: 64 bytes = four texture fetches (or two 256-bit loads) instead of the float node's five fetches of
+                    // 128 bytes; a bound byte q becomes the float 256 + q / 128 with one PRMT, the plane distance one FFMA (see k_pool, pt_pool.cuh)
+                    unsigned w0, w1, w2, w3, w4, w5, w6, w7, w8, w9, k0u, k1u, k2u, k3u;
+                    if (sc.bvh4q_tex) {
+                        const uint4 a0 = tex1Dfetch<uint4>(sc.bvh4q_tex, 4 * link), a1 = tex1Dfetch<uint4>(sc.bvh4q_tex, 4 * link + 1);
+                        const uint4 a2 = tex1Dfetch<uint4>(sc.bvh4q_tex, 4 * link + 2), a3 = tex1Dfetch<uint4>(sc.bvh4q_tex, 4 * link + 3);
+                        w0 = a0.x; w1 = a0.y; w2 = a0.z; w3 = a0.w; w4 = a1.x; w5 = a1.y; w6 = a1.z; w7 = a1.w;
+                        w8 = a2.x; w9 = a2.y; k0u = a3.x; k1u = a3.y; k2u = a3.z; k3u = a3.w;
+                    } else {
+                        const uint4 *nq = reinterpret_cast<const uint4 *>(sc.bvh4q) + 4 * (size_t)link;
+                        unsigned w10, w11;
+                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3), "=r"(w4), "=r"(w5), "=r"(w6), "=r"(w7) : "l"(nq));
+                        asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(w8), "=r"(w9), "=r"(w10), "=r"(w11), "=r"(k0u), "=r"(k1u), "=r"(k2u), "=r"(k3u) : "l"(nq + 2));
+                        (void)w10; (void)w11;
+                    }
+                    if (COUNT) wk.box += 4;
+                    const float Ax = __uint_as_float((w3 & 0xffu) << 23) * ix, Ay = __uint_as_float(((w3 >> 8) & 0xffu) << 23) * iy,
+                                Az = __uint_as_float(((w3 >> 16) & 0xffu) << 23) * iz;
+                    const float Cx = fmaf(-256.0f, Ax, fmaf(__uint_as_float(w0), ix, -ox)), Cy = fmaf(-256.0f, Ay, fmaf(__uint_as_float(w1), iy, -oy)),
+                                Cz = fmaf(-256.0f, Az, fmaf(__uint_as_float(w2), iz, -oz));
+                    const unsigned nxw = nx ? w5 : w4, fxw = nx ? w4 : w5, nyw = ny ? w7 : w6, fyw = ny ? w6 : w7, nzw = nz ? w9 : w8, fzw = nz ? w8 : w9;
+                    float d0, d1, d2, d3;
+#define WF_QF(word, sel) __uint_as_float(__byte_perm((word), 0x43800000u, (sel)))
+#define WF_QSLAB(dk, sel) do { float lo_ = fmaxf(fmaxf(fmaf(WF_QF(nxw, sel), Ax, Cx), fmaf(WF_QF(nyw, sel), Ay, Cy)), fmaf(WF_QF(nzw, sel), Az, Cz));   \
+                               float hi_ = fminf(fminf(fmaf(WF_QF(fxw, sel), Ax, Cx), fmaf(WF_QF(fyw, sel), Ay, Cy)), fmaf(WF_QF(fzw, sel), Az, Cz));   \
+                               lo_ = fmaxf(lo_ * 0.999996f, 0.0f); hi_ = fminf(hi_ * 1.000004f, best.t);                                                \
+                               dk = lo_ <= hi_ ? lo_ : PT_NO_HIT; } while (0)
+                    WF_QSLAB(d0, 0x7604); WF_QSLAB(d1, 0x7614); WF_QSLAB(d2, 0x7624); WF_QSLAB(d3, 0x7634);
+#undef WF_QSLAB
+#undef WF_QF
+                    int k0 = (int)k0u, k1 = (int)k1u, k2 = (int)k2u, k3 = (int)k3u;
+#define WF_CE(da, ka, db, kb) do { const bool sw_ = db < da; const float td_ = sw_ ? db : da; const int tk_ = sw_ ? kb : ka; \
+                                   db = sw_ ? da : db; kb = sw_ ? ka : kb; da = td_; ka = tk_; } while (0)
+                    WF_CE(d0, k0, d1, k1); WF_CE(d2, k2, d3, k3); WF_CE(d0, k0, d2, k2); WF_CE(d1, k1, d3, k3); WF_CE(d1, k1, d2, k2);
+#undef WF_CE
+                    if (d3 < PT_NO_HIT) WF_PUSH(k3, d3);
+                    if (d2 < PT_NO_HIT) WF_PUSH(k2, d2);
+                    if (d1 < PT_NO_HIT) WF_PUSH(k1, d1);
+                    if (WF_POSTPONE && d0 < PT_NO_HIT && k0 < 0 && pend == 0) { pend = k0; st = WF_POP; }
+                    else { link = k0; st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP; }
+                }
+                if (WIDE == 1 && st == WF_NODE) {
                     // 4-ary node (lbvh.cu): four slab tests, hits sorted by entry distance, nearest visited, rest pushed far-to-near.
                     // The near / far plane of every axis is picked by the SIGN of the ray direction when the row is fetched
                     // (rows 0/1 = lo.x/hi.x of the four children, 2/3 = y, 4/5 = z), not by a min/max per child and axis:
@@ -411,7 +459,7 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
                     if (WF_POSTPONE && d0 < PT_NO_HIT && k0 < 0 && pend == 0) { pend = k0; st = WF_POP; }
                     else { link = k0; st = d0 < PT_NO_HIT ? (k0 >= 0 ? WF_NODE : WF_LEAF) : WF_POP; }
                 }
-                if (!WIDE && st == WF_NODE) {
+                if (WIDE == 0 && st == WF_NODE) {
                     const float4 *nd = sc.bvh + 4 * (size_t)link;
                     float4 n0, n1, n2, n3;
                     if (sc.bvh_tex) {
@@ -487,6 +535,13 @@ __global__ void __launch_bounds__(PT_BLOCK, WF_MINB) k_wf_trace(const RenderPara
 // idling until the last long ray of the launch is done (the tail is about one ray latency, ~40 us: 7 % of a 2 M-path
 // iteration, 20 % of a 1 M-path one — the 8-GPU tile split).  Paths never move between sub-wavefronts and a pixel's samples
 // stay sequential, so the image does not depend on the number of sub-wavefronts.
+// which node format the trace kernel walks: 2 = quantised 4-ary (only when forced, ptb_set_quant_nodes(1): measured 3.37 vs 3.53 Grays/s on the
+// 1 M-triangle scene and 3.67 vs 3.96 on the 104 k one — this kernel's node fetches are already split over both L1 data pipes and the decode
+// costs it 24 more ALU instructions per node), 1 = float 4-ary, 0 = binary
+static int wf_wide_mode(const SceneDev &sc) {
+    if (sc.bvh4 == nullptr || sc.bvh_root < 0) return 0;
+    return (sc.bvh4q != nullptr && sc.quant_wf) ? 2 : 1;
+}
 #define WF_SUBS_MAX 4
 struct WfStreams { cudaStream_t s[WF_SUBS_MAX]; cudaEvent_t fork, join[WF_SUBS_MAX]; int *h_count; bool ok; };
 static WfStreams &wf_streams() {
@@ -522,14 +577,16 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     // persistent grid: exactly as many blocks as are resident at once (a block that has to wait for a slot would start
     // after the queue is drained and add a tail); 54-64 registers and 16-20 KB of shared memory give 8-9 per SM
     static const int want_per_sm = getenv("PTB_WF_BLOCKS") ? atoi(getenv("PTB_WF_BLOCKS")) : 9;
-    const bool wide = p.sc.bvh4 != nullptr && p.sc.bvh_root >= 0;
+    const int wide = wf_wide_mode(p.sc);
     int occ = 0;
     if (p.count_work) {
-        if (wide) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, true>, PT_BLOCK, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, PT_BLOCK, 0);
+        if (wide == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, 2>, PT_BLOCK, 0);
+        else if (wide == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, 1>, PT_BLOCK, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, 0>, PT_BLOCK, 0);
     } else {
-        if (wide) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, true>, PT_BLOCK, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, PT_BLOCK, 0);
+        if (wide == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, 2>, PT_BLOCK, 0);
+        else if (wide == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, 1>, PT_BLOCK, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, 0>, PT_BLOCK, 0);
     }
     const int per_sm = occ > 0 && occ < want_per_sm ? occ : want_per_sm;
     const int trace_blocks = sms * per_sm;
@@ -544,7 +601,7 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     // PTB_L2_PERSIST=1 (experiment): the wide-node array as a persisting L2 window on the trace streams, so that the path
     // state streaming through the shade kernel (136 B per path per iteration) does not evict the tree
     static const int l2_persist = getenv("PTB_L2_PERSIST") ? atoi(getenv("PTB_L2_PERSIST")) : 0;
-    if (l2_persist && wide && p.sc.n_nodes4 > 0) {
+    if (l2_persist && wide == 1 && p.sc.n_nodes4 > 0) {
         static int max_persist = -1, max_window = 0;
         if (max_persist < 0) {
             cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
@@ -584,11 +641,13 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
             cudaMemsetAsync(ctrl + b, 0, sizeof(int), sj[j]);
             cudaMemsetAsync(ctrl + 2, 0, sizeof(int), sj[j]);
             if (p.count_work) {
-                if (wide) k_wf_trace<true, true><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
-                else k_wf_trace<true, false><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                if (wide == 2) k_wf_trace<true, 2><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else if (wide == 1) k_wf_trace<true, 1><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else k_wf_trace<true, 0><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
             } else {
-                if (wide) k_wf_trace<false, true><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
-                else k_wf_trace<false, false><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                if (wide == 2) k_wf_trace<false, 2><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else if (wide == 1) k_wf_trace<false, 1><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
+                else k_wf_trace<false, 0><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
             }
             k_wf_shade<<<(host_count[j] + 255) / 256, 256, 0, sj[j]>>>(p, qa, ctrl + a, qb, ctrl + b);
             launches += 2;

@@ -139,7 +139,8 @@ struct State {
     unsigned long long launches = 0;
     PendingGen pending;
     int regen_min = 8;                 // k_render: batch path regeneration until this many lanes of a warp wait (PTB_REGEN_MIN)
-    int quant_nodes = 1;               // pool kernel: traverse the 64-byte quantised wide nodes (PTB_QUANT_NODES=0: the 128-byte float nodes)
+    size_t quant_min_bytes = 8u << 20;
+    int quant_nodes = 2;               // pool kernel: traverse the 64-byte quantised wide nodes (PTB_QUANT_NODES=0: the 128-byte float nodes)
     int auto_pool = 2;                 // PTB_PIPE_AUTO on LBVH scenes: 0 = the wavefront, 1 = the pool kernel, 2 = by owned pixels (PTB_AUTO_POOL)
     long long auto_pool_pixels = 1500000;   // ... the pool kernel up to this many pixels on this GPU (PTB_AUTO_POOL_PIXELS)
 };
@@ -417,7 +418,12 @@ int make_params(RenderParams &p, size_t W, size_t H, int spp, bool from_rays) {
         // the 4-ary traversal pushes up to 3 entries per level: usable when the stack bound (64) covers the tree
         const int wide_levels = (s.lbvh.max_depth + 1) / 2;
         p.sc.bvh4 = (G.wide_bvh && s.lbvh.n_nodes4 > 0 && 3 * wide_levels + 1 <= 64) ? s.lbvh.bvh4 : nullptr;
-        p.sc.bvh4q = (p.sc.bvh4 && G.quant_nodes) ? s.lbvh.bvh4q : nullptr;
+        // node format (pool kernel; the wavefront keeps the float nodes unless forced): the 64-byte quantised nodes pay when the float nodes (128 bytes each) do not sit comfortably in L1 / L2 next to
+        // the triangles and the path state (1 M triangles: 30 MB of nodes, +20 %); on small trees their slightly wider boxes cost more
+        // than the bytes return (104 k triangles: 3 MB, -5 %) — profiles/r02_quant_nodes.txt.  2 = by size, 1 = always, 0 = never
+        const bool quant = G.quant_nodes == 1 || (G.quant_nodes == 2 && (size_t)s.lbvh.n_nodes4 * 128 > G.quant_min_bytes);
+        p.sc.bvh4q = (p.sc.bvh4 && quant) ? s.lbvh.bvh4q : nullptr;
+        p.sc.quant_wf = G.quant_nodes == 1;
         p.sc.bvh4q_tex = G.tex_nodes ? s.lbvh.bvh4q_tex : 0;
         p.sc.n_nodes4 = s.lbvh.n_nodes4;
         p.sc.srec = fastm ? s.lbvh.rf : s.lbvh.rq;
@@ -744,7 +750,7 @@ int ptb_init(int device_ordinal) {
     if ((env = getenv("PTB_LBVH_BIG"))) G.lbvh_big = (float)atof(env);
     if ((env = getenv("PTB_AUTO_POOL"))) G.auto_pool = atoi(env) < 0 ? 0 : (atoi(env) > 2 ? 2 : atoi(env));
     if ((env = getenv("PTB_AUTO_POOL_PIXELS"))) G.auto_pool_pixels = atoll(env);
-    if ((env = getenv("PTB_QUANT_NODES"))) G.quant_nodes = atoi(env) ? 1 : 0;
+    if ((env = getenv("PTB_QUANT_NODES"))) G.quant_nodes = atoi(env) < 0 ? 0 : (atoi(env) > 2 ? 2 : atoi(env));
     if ((env = getenv("PTB_REGEN_MIN"))) G.regen_min = atoi(env) < 1 ? 1 : (atoi(env) > 32 ? 32 : atoi(env));
     return PTB_SUCCESS;
 }
@@ -1069,7 +1075,8 @@ int ptb_set_pipeline(int pipe) {
     return PTB_SUCCESS;
 }
 int ptb_set_quant_nodes(int on) {
-    G.quant_nodes = on ? 1 : 0;
+    if (on < 0 || on > 2) return PTB_ERR_INVALID_VALUE;
+    G.quant_nodes = on;
     return PTB_SUCCESS;
 }
 int ptb_set_wf_subs(int n) {

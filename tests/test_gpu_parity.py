@@ -212,6 +212,20 @@ def test_spheres100k_fast_flavour_against_the_reference(ptb, spheres_ref, pipeli
     assert (rnds == spheres_ref["rnds"]).mean() >= 0.999
 
 
+@pytest.mark.parametrize("pipeline", [capi.PIPE_WAVEFRONT, capi.PIPE_POOL])
+def test_quantised_wide_nodes_do_not_change_a_bit(ptb, spheres_ref, mixed_ref, pipeline):
+    """the 64-byte quantised 4-ary nodes forced on for trees the default would walk as float nodes: same image, same RNG states"""
+    try:
+        ptb.set_quant_nodes(1)
+        for ref, spp in ((spheres_ref, 4), (mixed_ref, 8)):
+            colors, rnds = render(ptb, ref, capi.ACCEL_LBVH, capi.MATH_PARITY, "render_spp", spp=spp, pipeline=pipeline)
+            st = util.compare(colors, ref["colors"])
+            assert st["bit_equal_frac"] >= 1.0 - 1e-4, st
+            assert (rnds == ref["rnds"]).mean() >= 1.0 - 1e-4
+    finally:
+        ptb.set_quant_nodes(2)
+
+
 @pytest.mark.parametrize("mode", ["fused_launches", "render_spp"])
 def test_pool_kernel_on_cornell_is_bit_identical(ptb, cornell_ref, mode):
     """the persistent pool kernel (PTB_PIPE_POOL) forced onto the 32-triangle scene through the LBVH: per-sample launches

@@ -81,12 +81,12 @@ def test_every_structure_equals_brute_force_on_random_rays(ptb, math, scene, dup
         ptb.set_merge_prims(0)                    # (fast flavour: plain triangles first — same test code as brute force, so exact)
         for accel, pipe in ((capi.ACCEL_LBVH, capi.PIPE_MEGAKERNEL), (capi.ACCEL_LBVH, capi.PIPE_WAVEFRONT), (capi.ACCEL_LBVH, capi.PIPE_POOL)):
             ptb.set_accel(accel); ptb.set_pipeline(pipe)
-            assert same(ptb.closest_hit(o, dirs), want), (accel, pipe)
-        ptb.set_quant_nodes(0)                    # the pool kernel over the 128-byte float nodes instead of the 64-byte quantised ones
-        assert same(ptb.closest_hit(o, dirs), want), "pool, float nodes"
+            for quant in (1, 0):                  # 64-byte quantised wide nodes forced on, then the 128-byte float nodes (the default picks by tree size)
+                ptb.set_quant_nodes(quant)
+                assert same(ptb.closest_hit(o, dirs), want), (accel, pipe, quant)
     finally:
         ptb.set_merge_prims(1)
-        ptb.set_quant_nodes(1)
+        ptb.set_quant_nodes(2)
     if math == capi.MATH_FAST:
         # shipping configuration: the outlier list is scanned as merged quads, a hit on either half reports the pair's lower
         # index and t comes from the shared plane — same surface, same material, t within rounding
