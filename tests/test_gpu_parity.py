@@ -226,6 +226,21 @@ def test_quantised_wide_nodes_do_not_change_a_bit(ptb, spheres_ref, mixed_ref, p
         ptb.set_quant_nodes(2)
 
 
+def test_fast_flavour_pipelines_agree_to_rounding_parity_flavour_to_the_bit(ptb, spheres_ref):
+    """pool kernel vs wavefront on the same scene: the parity flavour (no FMA contraction) is the same bits through both; the fast
+    flavour is the same SOURCE compiled into two kernels whose FMA contraction may differ, so it is held to the fast tolerance only"""
+    out = {}
+    for math in (capi.MATH_PARITY, capi.MATH_FAST):
+        for pipe in (capi.PIPE_WAVEFRONT, capi.PIPE_POOL):
+            out[math, pipe] = render(ptb, spheres_ref, capi.ACCEL_LBVH, math, "render_spp", spp=4, pipeline=pipe)
+    a, b = out[capi.MATH_PARITY, capi.PIPE_WAVEFRONT], out[capi.MATH_PARITY, capi.PIPE_POOL]
+    assert util.compare(a[0], b[0])["bit_equal_frac"] == 1.0 and (a[1] == b[1]).all()
+    a, b = out[capi.MATH_FAST, capi.PIPE_WAVEFRONT], out[capi.MATH_FAST, capi.PIPE_POOL]
+    st = util.compare(a[0], b[0])
+    print("fast flavour, pool vs wavefront:", st)
+    assert st["frac_rel_le_1e-4"] >= 0.999 and st["rmse_over_mean"] <= 0.01, st
+
+
 @pytest.mark.parametrize("mode", ["fused_launches", "render_spp"])
 def test_pool_kernel_on_cornell_is_bit_identical(ptb, cornell_ref, mode):
     """the persistent pool kernel (PTB_PIPE_POOL) forced onto the 32-triangle scene through the LBVH: per-sample launches
