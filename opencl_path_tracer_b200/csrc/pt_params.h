@@ -83,7 +83,7 @@ struct RenderParams {
     unsigned long long *counters; // PT_CNT_WORDS words
     // wavefront pipeline scratch (pt_wavefront.cuh), one path per pixel, allocated by ptb_abi.cu; null = megakernel only
     float4 *wf_ray0, *wf_ray1;    // (P.xyz, D.x) (D.y, D.z, t_hit, bits(tri))
-    float4 *wf_state;             // 6 planes of W*H float4: throughputs, sample colour, accumulator, rng, counters
+    float4 *wf_state;             // WF_PLANES planes of W*H float4 (pt_wavefront.cuh wf_store_hot): 0-2 hot, 3 tally, 4 colour, 5 parity fR.yz
     int *wf_queue[2];             // active pixel ids, double buffered
     int *wf_ctrl;                 // [0],[1] queue lengths, [2] fetch cursor of the trace kernel, [3] spare
 };

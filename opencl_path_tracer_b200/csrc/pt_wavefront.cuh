@@ -1,6 +1,6 @@
 // pt_wavefront.cuh — wavefront organisation of the same path (included inside namespace PT_NS).
 //
-// One PATH per pixel lives in global memory (ray 32 B + state 96 B).  A render is a sequence of
+// One PATH per pixel lives in global memory (ray 32 B + state 80-88 B, of which a path step touches 48-56 B: wf_store_hot).  A render is a sequence of
 // iterations; each iteration advances every active path by one ray:
 //     k_wf_trace   persistent warps; every lane pulls the next queued path as soon as its traversal
 //                  ends (warp-aggregated atomic fetch), so no lane waits for a neighbour's long
@@ -18,31 +18,60 @@
 // so the result is bit-identical to the other pipelines in the parity flavour.
 // Iterations needed: at most spp * iterations (every active path consumes one ray per iteration).
 
-#define WF_PLANES 6
+#define WF_PLANES 6                      // float4 planes of W*H reserved per frame (ptb_abi.cu, pt_pool.cuh size their scratch by it)
 struct WfPath {
     Path ps;
     V3 acc;
     uint32_t rng;
     int s, depth;
 };
-PT_DEV void wf_store_state(const RenderParams &p, int i, const WfPath &w) {
+// Path state in global memory, split by HOW OFTEN a path step needs it (round-1 verdict: 96 B read + 96 B written per step).
+//   hot   (every step): the throughput factors fL, fB, fS, the RNG state, depth | inside-glass flag — three float4 planes, 48 B.
+//         The parity flavour also keeps fR (the fast one folds it into fS, shade_hit): its x in the spare word, y z in a float2 plane.
+//   tally (sample end only, ~1 step in 3): running mean / sum of the pixel and the sample index — one float4 plane.
+//   color (sample end, emitter hits, flat preview): the sample's radiance so far — one float4 plane.
+// Planes 0-2 hot, 3 tally, 4 color, first half of 5: the parity flavour's float2 plane.
+PT_DEV void wf_store_hot(const RenderParams &p, int i, const WfPath &w) {
     const size_t n = (size_t)p.W * p.H;
     float4 *st = p.wf_state + i;
+    const int di = w.depth | (w.ps.in ? (int)0x80000000 : 0);
     st[0 * n] = make_float4(w.ps.fL.x, w.ps.fL.y, w.ps.fL.z, w.ps.fB.x);
     st[1 * n] = make_float4(w.ps.fB.y, w.ps.fB.z, w.ps.fS.x, w.ps.fS.y);
-    st[2 * n] = make_float4(w.ps.fS.z, w.ps.fR.x, w.ps.fR.y, w.ps.fR.z);
-    st[3 * n] = make_float4(w.ps.color.x, w.ps.color.y, w.ps.color.z, __uint_as_float(w.rng));
-    st[4 * n] = make_float4(w.acc.x, w.acc.y, w.acc.z, __int_as_float(w.s));
-    st[5 * n] = make_float4(__int_as_float(w.depth), __int_as_float(w.ps.in ? 1 : 0), 0.0f, 0.0f);
+#if PT_PARITY
+    st[2 * n] = make_float4(w.ps.fS.z, __uint_as_float(w.rng), __int_as_float(di), w.ps.fR.x);
+    reinterpret_cast<float2 *>(p.wf_state + 5 * n)[i] = make_float2(w.ps.fR.y, w.ps.fR.z);
+#else
+    st[2 * n] = make_float4(w.ps.fS.z, __uint_as_float(w.rng), __int_as_float(di), 0.0f);
+#endif
 }
-PT_DEV void wf_load_state(const RenderParams &p, int i, WfPath &w) {
+PT_DEV void wf_load_hot(const RenderParams &p, int i, WfPath &w) {
     const size_t n = (size_t)p.W * p.H;
     const float4 *st = p.wf_state + i;
-    const float4 a = st[0 * n], b = st[1 * n], c = st[2 * n], d = st[3 * n], e = st[4 * n], f = st[5 * n];
-    w.ps.fL = v3(a.x, a.y, a.z); w.ps.fB = v3(a.w, b.x, b.y); w.ps.fS = v3(b.z, b.w, c.x); w.ps.fR = v3(c.y, c.z, c.w);
-    w.ps.color = v3(d.x, d.y, d.z); w.rng = __float_as_uint(d.w);
+    const float4 a = st[0 * n], b = st[1 * n], c = st[2 * n];
+    w.ps.fL = v3(a.x, a.y, a.z); w.ps.fB = v3(a.w, b.x, b.y); w.ps.fS = v3(b.z, b.w, c.x);
+    w.rng = __float_as_uint(c.y);
+    const int di = __float_as_int(c.z);
+    w.depth = di & 0x7fffffff; w.ps.in = di < 0;
+#if PT_PARITY
+    const float2 r = reinterpret_cast<const float2 *>(p.wf_state + 5 * n)[i];
+    w.ps.fR = v3(c.w, r.x, r.y);
+#else
+    w.ps.fR = v3(1.0f, 1.0f, 1.0f);
+#endif
+}
+PT_DEV void wf_store_tally(const RenderParams &p, int i, const WfPath &w) {
+    p.wf_state[3 * (size_t)p.W * p.H + i] = make_float4(w.acc.x, w.acc.y, w.acc.z, __int_as_float(w.s));
+}
+PT_DEV void wf_load_tally(const RenderParams &p, int i, WfPath &w) {
+    const float4 e = p.wf_state[3 * (size_t)p.W * p.H + i];
     w.acc = v3(e.x, e.y, e.z); w.s = __float_as_int(e.w);
-    w.depth = __float_as_int(f.x); w.ps.in = __float_as_int(f.y) != 0;
+}
+PT_DEV void wf_store_color(const RenderParams &p, int i, const WfPath &w) {
+    p.wf_state[4 * (size_t)p.W * p.H + i] = make_float4(w.ps.color.x, w.ps.color.y, w.ps.color.z, 0.0f);
+}
+PT_DEV void wf_load_color(const RenderParams &p, int i, WfPath &w) {
+    const float4 d = p.wf_state[4 * (size_t)p.W * p.H + i];
+    w.ps.color = v3(d.x, d.y, d.z);
 }
 PT_DEV void wf_store_ray(const RenderParams &p, int i, V3 P, V3 D, const Closest &best) {
     p.wf_ray0[i] = make_float4(P.x, P.y, P.z, D.x);
@@ -191,7 +220,9 @@ __global__ void __launch_bounds__(256) k_wf_init(const RenderParams p, const int
             Closest best;
             wf_big_scan(p, s_big, n_big_pairs, P, D, best, wk);
             wf_store_ray(p, i, P, D, best);
-            wf_store_state(p, i, w);
+            wf_store_hot(p, i, w);
+            wf_store_tally(p, i, w);
+            wf_store_color(p, i, w);
         } else wf_finish_pixel(p, i, w);
     }
     wf_push(p.wf_queue[0] + (size_t)sub * sub_cap, p.wf_ctrl + 4 * sub, keep, i);
@@ -220,30 +251,37 @@ __global__ void __launch_bounds__(256, WF_SHADE_MINB) k_wf_shade(const RenderPar
         const float t = r1.z;
         const int tri = __float_as_int(r1.w);
         WfPath w;
-        wf_load_state(p, i, w);
+        wf_load_hot(p, i, w);
         const V3 eye = v3(p.cam.eye.x, p.cam.eye.y, p.cam.eye.z);
-        bool alive = true;
+        const bool hit = t < PT_NO_HIT;
+        // the sample ends with this step on a miss (prog.cl:367-376) or at the last bounce: known before the material is,
+        // so the planes only a finished sample needs are requested here, beside the triangle's
+        const bool ends = !hit || w.depth + 1 >= p.iterations;
+        if (ends) { wf_load_tally(p, i, w); wf_load_color(p, i, w); }
         wk.rays++;
-        if (t < PT_NO_HIT) {
+        if (hit) {
             V3 hitP = rayP + rayD * t;                               // prog.cl:107
             V3 hitN = tri_normal(ldg4(sc.q0 + tri), ldg4(sc.q1 + tri), ldg4(sc.q2 + tri));
             Mat m = load_material(sc.mats, (int)__ldg(sc.mati + tri));
+            const bool lit = m.type == 3 || p.iterations == 1;       // the only steps that touch the sample's radiance (shade_hit)
+            if (lit && !ends) wf_load_color(p, i, w);
             shade_hit(m, hitP, hitN, rayP, rayD, w.rng, w.ps, eye, p.iterations);
-            if (++w.depth >= p.iterations) alive = false;
-        } else {
-            alive = false;                                           // miss: break, prog.cl:367-376
+            if (lit && !ends) wf_store_color(p, i, w);
+            ++w.depth;
         }
-        if (!alive) {                                                // sample finished, prog.cl:379
+        bool alive = !ends;
+        if (ends) {                                                  // sample finished, prog.cl:379
             if (p.sum_mode) w.acc = w.acc + w.ps.color; else w.acc = pt_mean_step(w.acc, w.ps.color, w.s);
             ++w.s;
             wk.samples++;
             alive = wf_next_sample(p, i, w, rayP, rayD, p.sample0 + p.spp, wk);
+            if (alive) { wf_store_tally(p, i, w); wf_store_color(p, i, w); }
         }
         if (alive) {
             Closest best;
             wf_big_scan(p, s_big, n_big_pairs, rayP, rayD, best, wk);
             wf_store_ray(p, i, rayP, rayD, best);
-            wf_store_state(p, i, w);
+            wf_store_hot(p, i, w);
         } else wf_finish_pixel(p, i, w);
         keep = alive;
     }
@@ -568,8 +606,14 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     int subs = ws.ok ? (want_subs < 1 ? 1 : want_subs > WF_SUBS_MAX ? WF_SUBS_MAX : want_subs) : 1;
     if (subs > init_blocks) subs = init_blocks > 0 ? init_blocks : 1;
     const int sub_cap = ((init_blocks + subs - 1) / subs) * 256;          // queue slots per sub-wavefront (ptb_abi.cu sizes the queues for it)
-    cudaMemsetAsync(p.wf_ctrl, 0, 4 * WF_SUBS_MAX * sizeof(int), st);
+    // every CUDA call of the loop is checked: the first failure ends the loop, -1 goes back to ptb_render (which reports the
+    // CUDA error by name; a failed call leaves it in cudaGetLastError)
+    bool failed = false;
+#define WF_CK(call) do { if ((call) != cudaSuccess) failed = true; } while (0)
+    WF_CK(cudaMemsetAsync(p.wf_ctrl, 0, 4 * WF_SUBS_MAX * sizeof(int), st));
     k_wf_init<<<init_blocks, 256, 0, st>>>(p, subs, sub_cap);
+    WF_CK(cudaPeekAtLastError());
+    if (failed) return -1;
     ++launches;
     int sms = 148, dev = 0;
     cudaGetDevice(&dev);
@@ -623,13 +667,13 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
         cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
         for (int j = 1; j < subs; ++j) cudaStreamSetAttribute(ws.s[j], cudaStreamAttributeAccessPolicyWindow, &av);
     }
-    if (subs > 1) cudaEventRecord(ws.fork, st);
+    if (subs > 1) WF_CK(cudaEventRecord(ws.fork, st));
     for (int j = 0; j < subs; ++j) {
-        if (j > 0) { sj[j] = ws.s[j]; cudaStreamWaitEvent(sj[j], ws.fork, 0); }
+        if (j > 0) { sj[j] = ws.s[j]; WF_CK(cudaStreamWaitEvent(sj[j], ws.fork, 0)); }
         host_count[j] = sub_cap;
         live[j] = true;
     }
-    for (long long it = 0; it < max_iters; ++it) {
+    for (long long it = 0; it < max_iters && !failed; ++it) {
         const int a = (int)(it & 1), b = a ^ 1;
         bool any = false;
         for (int j = 0; j < subs; ++j) {
@@ -638,8 +682,8 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
             int *ctrl = p.wf_ctrl + 4 * j;
             int *qa = p.wf_queue[a] + (size_t)j * sub_cap, *qb = p.wf_queue[b] + (size_t)j * sub_cap;
             // next queue length and the fetch cursor start at zero
-            cudaMemsetAsync(ctrl + b, 0, sizeof(int), sj[j]);
-            cudaMemsetAsync(ctrl + 2, 0, sizeof(int), sj[j]);
+            WF_CK(cudaMemsetAsync(ctrl + b, 0, sizeof(int), sj[j]));
+            WF_CK(cudaMemsetAsync(ctrl + 2, 0, sizeof(int), sj[j]));
             if (p.count_work) {
                 if (wide == 2) k_wf_trace<true, 2><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
                 else if (wide == 1) k_wf_trace<true, 1><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
@@ -649,24 +693,28 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
                 else if (wide == 1) k_wf_trace<false, 1><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
                 else k_wf_trace<false, 0><<<trace_blocks, PT_BLOCK, 0, sj[j]>>>(p, qa, ctrl + a, ctrl + 2, tune);
             }
+            WF_CK(cudaPeekAtLastError());
             k_wf_shade<<<(host_count[j] + 255) / 256, 256, 0, sj[j]>>>(p, qa, ctrl + a, qb, ctrl + b);
+            WF_CK(cudaPeekAtLastError());
             launches += 2;
         }
         if (!any) break;
         if ((it & 15) == 15) {                     // every 16 iterations: learn the real queue lengths (shrinks the grids, ends early)
             for (int j = 0; j < subs; ++j)
-                if (live[j]) cudaMemcpyAsync(ws.ok ? ws.h_count + j : host_count + j, p.wf_ctrl + 4 * j + b, sizeof(int), cudaMemcpyDeviceToHost, sj[j]);
+                if (live[j]) WF_CK(cudaMemcpyAsync(ws.ok ? ws.h_count + j : host_count + j, p.wf_ctrl + 4 * j + b, sizeof(int), cudaMemcpyDeviceToHost, sj[j]));
             for (int j = 0; j < subs; ++j) {
                 if (!live[j]) continue;
-                cudaStreamSynchronize(sj[j]);
+                WF_CK(cudaStreamSynchronize(sj[j]));
+                if (failed) break;
                 if (ws.ok) host_count[j] = ws.h_count[j];
                 if (host_count[j] == 0) live[j] = false;
             }
         }
     }
     for (int j = 1; j < subs; ++j) {               // join: the caller's stream continues after every sub-wavefront
-        cudaEventRecord(ws.join[j], sj[j]);
-        cudaStreamWaitEvent(st, ws.join[j], 0);
+        WF_CK(cudaEventRecord(ws.join[j], sj[j]));
+        WF_CK(cudaStreamWaitEvent(st, ws.join[j], 0));
     }
-    return launches;
+#undef WF_CK
+    return failed ? -1 : launches;
 }

@@ -539,6 +539,7 @@ int run_wavefront(RenderParams &p) {
     p.wf_ctrl = (int *)b;
     int k = G.math == PTB_MATH_PARITY ? pt_parity::launch_wavefront(p, S()) : pt_fast::launch_wavefront(p, S());
     CUDA_OK(cudaGetLastError());
+    if (k < 0) return fail(PTB_ERR_DEVICE, "wavefront: a CUDA call of the iteration loop failed");
     G.launches += (unsigned long long)k;
     return PTB_SUCCESS;
 }
