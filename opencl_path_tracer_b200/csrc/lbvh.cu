@@ -31,6 +31,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "lbvh.h"
 
@@ -236,22 +237,23 @@ __global__ void k_ploc_init(int m, const float4 *leaf_lo, const float4 *leaf_hi,
 // nearest neighbour of every cluster within PLOC_R positions.  Candidate pairs are compared by (area, not the aligned pair i^1, distance,
 // lower index): a strict total order over unordered pairs, symmetric in the pair, so the globally smallest pair is chosen by both of its
 // clusters — at least one merge per round, also when all areas are equal (a stack of identical triangles).
+template <int R>
 __global__ void __launch_bounds__(256) k_ploc_nn(int m, const float4 *clo, const float4 *chi, int *nn) {
-    __shared__ float4 slo[256 + 2 * PLOC_R], shi[256 + 2 * PLOC_R];
-    const int base = blockIdx.x * 256 - PLOC_R;
-    for (int t = threadIdx.x; t < 256 + 2 * PLOC_R; t += 256) {
+    __shared__ float4 slo[256 + 2 * R], shi[256 + 2 * R];
+    const int base = blockIdx.x * 256 - R;
+    for (int t = threadIdx.x; t < 256 + 2 * R; t += 256) {
         const int g = base + t;
         if (g >= 0 && g < m) { slo[t] = clo[g]; shi[t] = chi[g]; }
     }
     __syncthreads();
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= m) return;
-    const int li = threadIdx.x + PLOC_R;
+    const int li = threadIdx.x + R;
     const float4 mlo = slo[li], mhi = shi[li];
     float best = 4.0e38f;
     int bestj = -1, best_na = 2, best_d = 1 << 30, best_mn = 1 << 30;
 #pragma unroll
-    for (int o = -PLOC_R; o <= PLOC_R; ++o) {
+    for (int o = -R; o <= R; ++o) {
         if (o == 0) continue;
         const int j = i + o;
         if (j < 0 || j >= m) continue;
@@ -681,9 +683,12 @@ int lbvh_build(Lbvh *b, const float4 *q0, const float4 *q1, const float4 *q2, co
             k_ploc_init<<<(m + 255) / 256, 256, 0, st>>>(m, b->leaf_lo, b->leaf_hi, t.clo[0], t.chi[0]);
             int cur = 0, mc = m, next_id = m - 2, rounds = 0;
             unsigned long long h_last[2];
+            static const int ploc_r = getenv("PTB_PLOC_R") ? atoi(getenv("PTB_PLOC_R")) : PLOC_R;      // search radius: 8 (default), 16, 32
             while (mc > 1 && rounds < 1024) {
                 const int g = (mc + 255) / 256;
-                k_ploc_nn<<<g, 256, 0, st>>>(mc, t.clo[cur], t.chi[cur], nn);
+                if (ploc_r >= 32) k_ploc_nn<32><<<g, 256, 0, st>>>(mc, t.clo[cur], t.chi[cur], nn);
+                else if (ploc_r >= 16) k_ploc_nn<16><<<g, 256, 0, st>>>(mc, t.clo[cur], t.chi[cur], nn);
+                else k_ploc_nn<PLOC_R><<<g, 256, 0, st>>>(mc, t.clo[cur], t.chi[cur], nn);
                 k_ploc_flag<<<g, 256, 0, st>>>(mc, nn, flags);
                 CK(cub::DeviceScan::ExclusiveSum(t.scan_tmp, scan_bytes, flags, t.pscan, mc, st));
                 k_ploc_apply<<<g, 256, 0, st>>>(mc, next_id, nn, flags, t.pscan, t.clo[cur], t.chi[cur], t.clo[cur ^ 1], t.chi[cur ^ 1], (int2 *)b->child,
