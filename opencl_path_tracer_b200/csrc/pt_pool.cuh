@@ -63,6 +63,10 @@ PT_DEV float pool_rcp(float d) { return fabsf(d) > 1e-25f ? 1.0f / d : copysignf
 
 // Path state of a slot: 24 words as THREE 32-byte chunks (planes of total_slots chunks), each one 256-bit access: 3 loads + 3 stores
 // per shaded ray on the LSU pipe instead of 6 + 6 sixteen-byte ones.  Through L2 (.cg): another lane of the warp may serve the slot next.
+// MEASURED AND DROPPED (profiles/r02_pool_state_split.txt): the wavefront's hot / cold split (two chunks every step, the third — running mean,
+// sample index, sample radiance — only when a sample ends or an emitter is hit) is 2.5 % SLOWER here (3.76 vs 3.86 Grays/s on the 104 k scene,
+// 2.94 vs 3.00 on a 1/8 share of the 1 M scene), with the third load conditional or not: the state lives in L2 next to the warp, its bytes
+// are not what the shade phase waits for, and the extra predicates and the dirty flag cost issue slots in the kernel's longest phase.
 PT_DEV void pool_st8(float4 *p, float a, float b, float c, float d, float e, float f, float g, float h) {
     asm volatile("st.global.cg.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d), "f"(e), "f"(f), "f"(g), "f"(h) : "memory");
 }
