@@ -643,7 +643,7 @@ int launch_wavefront(const RenderParams &p, cudaStream_t st) {
     bool live[WF_SUBS_MAX];
     sj[0] = st;
     // PTB_L2_PERSIST=1 (experiment): the wide-node array as a persisting L2 window on the trace streams, so that the path
-    // state streaming through the shade kernel (136 B per path per iteration) does not evict the tree
+    // state streaming through the shade kernel (80-110 B per path per iteration) does not evict the tree
     static const int l2_persist = getenv("PTB_L2_PERSIST") ? atoi(getenv("PTB_L2_PERSIST")) : 0;
     if (l2_persist && wide == 1 && p.sc.n_nodes4 > 0) {
         static int max_persist = -1, max_window = 0;
