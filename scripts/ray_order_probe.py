@@ -4,7 +4,7 @@ wavefront trace kernel): the same 2 M bounce-like rays (origins on the scene's s
 four orders — A: by Morton code of the origin (what the queue's pixel order gives a bounce), B: by direction octant, then origin
 Morton, C: by coarse origin cell (4096 cells), then octant, then fine Morton, D: shuffled.  Host clock around blocking calls.
   python scripts/ray_order_probe.py [scene ...]"""
-import sys, time
+import os, sys, time
 import numpy as np
 sys.path.insert(0, ".")
 from opencl_path_tracer_b200 import capi, host, scenes
@@ -53,10 +53,10 @@ def main():
             for label, idx in orders.items():
                 rays = np.zeros((n, 8), dtype=np.float32); rays[:, 0:3], rays[:, 4:7] = o[idx], dirs[idx]
                 h_rays, h_out = ptb.upload(rays), ptb.alloc(n * 8)
-                for _ in range(3):
+                for _ in range(int(os.environ.get('PROBE_WARM', 3))):
                     ptb.lib.ptb_closest_hit(h_rays, n, h_out)
                 ptb.finish(); t0 = time.perf_counter()
-                reps = 10
+                reps = int(os.environ.get('PROBE_REPS', 10))
                 for _ in range(reps):
                     ptb.lib.ptb_closest_hit(h_rays, n, h_out)
                 ptb.finish(); dt = (time.perf_counter() - t0) / reps
